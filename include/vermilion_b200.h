@@ -1,0 +1,184 @@
+/*
+ * vermilion_b200.h — C ABI of libvermilion_b200.so, the B200 (sm_100a) engine for
+ * Vermilion's ray-tracing hot path.
+ *
+ * The reference (CasperTheCat/Vermilion) has no FFI or plugin registry; the seam the
+ * path sits behind is the C++ virtual interface Vermilion::Integrator::Render
+ * (core/integrators/integrators.h:11-16) plus the accelerator seam
+ * BVH::getIntersection (core/accelerators/bvh.h:29-30) and MeshEngine::RayCast
+ * (core/engines/meshEngine.h:113-114). Each entry point below names the reference
+ * interface it replaces. The C++ adapter vermilion_b200/host/b200_pathtracer.{h,cpp}
+ * (class B200PathTracer : Vermilion::Integrator) is the reference-side binding; see
+ * INTEGRATION.md.
+ *
+ * Conventions: every call returns vmn_status (0 = OK); no exceptions or callbacks
+ * cross the ABI; host pointers are borrowed for the duration of the call only;
+ * `_device` variants take CUDA device pointers valid on the context's device; the
+ * context owns all other device memory. One context drives ONE device (multi-GPU =
+ * one process/context per GPU, the film buffer exchanged by the host with NCCL). A
+ * context is not thread-safe. There is no CPU fallback: without a CUDA device
+ * vmn_create fails with VMN_ERR_CUDA.
+ *
+ * All file:line citations are into the reference tree.
+ */
+#ifndef VERMILION_B200_H
+#define VERMILION_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built -fvisibility=hidden; these are its only exports */
+#endif
+
+#define VMN_ABI_VERSION 1
+
+typedef enum {
+    VMN_OK = 0,
+    VMN_ERR_INVALID = 1, /* bad argument */
+    VMN_ERR_CUDA = 2,    /* CUDA runtime / launch failure, or no device */
+    VMN_ERR_OOM = 3,     /* device or host allocation failed */
+    VMN_ERR_STATE = 4    /* call order violated (e.g. render before commit) */
+} vmn_status;
+
+typedef struct vmn_ctx vmn_ctx;
+
+typedef struct {
+    int32_t device;        /* CUDA device ordinal */
+    uint32_t flags;        /* VMN_CFG_* */
+    uint64_t max_paths;    /* wavefront pool size (paths in flight); 0 = default 4 Mi */
+    void* stream;          /* cudaStream_t to launch on; NULL = a stream the context creates */
+} vmn_config;
+#define VMN_CFG_COUNTERS 1u /* keep per-ray node/triangle visit counters (slower; for B_ray) */
+
+/* 32-byte ray = core/accelerators/Ray.h:4-11 without inv_d. pads are ignored. */
+typedef struct { float o[3]; float pad0; float d[3]; float pad1; } vmn_ray;
+
+/* 16-byte closest-hit record = IntersectionInfo (core/accelerators/IntersectionInfo.h:6-10)
+ * with the Object* replaced by the canonical triangle id (running face index of
+ * MeshEngine::createBVH, meshEngine.cpp:660-717) and (u,v) = the barycentric weights
+ * (w1,w2) Triangle::getNormal derives from the hit point (triangle.cpp:67-78).
+ * Miss: tri = VMN_MISS, t = 999999999.f (bvh.cpp:48), u = v = 0. */
+typedef struct { float t; float u; float v; uint32_t tri; } vmn_hit;
+#define VMN_MISS 0xFFFFFFFFu
+
+/* 64-byte record of every output of MeshEngine::RayCast (meshEngine.cpp:239-509). */
+#define VMN_RC_HIT 1u      /* RayCast's return value */
+#define VMN_RC_MATERIAL 2u /* *ppImpactMaterial != nullptr (a triangle lies on the ray, :502-503) */
+typedef struct {
+    float P[3];
+    float dist;
+    float N[3];
+    uint32_t flags;
+    float uv[2];
+    float Le[3];
+    uint32_t tri;
+    uint32_t pad[2];
+} vmn_raycast_rec;
+
+/* One analytic sphere of MeshEngine::RayCast (meshEngine.cpp:377-500). The reference
+ * hard-codes eight; vmn_reference_spheres() returns them in its test order. */
+#define VMN_SPH_FLIP_NORMAL 1u /* N = -normalize(P - normal_center) */
+typedef struct {
+    float center[3];
+    float radius;
+    float emission[3];
+    uint32_t flags;
+    float normal_center[3]; /* the reference measures emitter normals from other points (:385,:418) */
+    float pad;
+} vmn_sphere;
+
+/* Camera as Vermilion::Camera holds it after its constructor (camera.cpp:34-56):
+ * rotation in radians with x,y already negated. */
+typedef struct {
+    uint32_t width, height;
+    float position[3];
+    float rotation[3];
+    float dist_to_film;
+    float sensor_x, sensor_y;
+    uint32_t spp; /* uSamplesPerPixel */
+} vmn_camera;
+
+enum { VMN_MODE_COMPAT = 0, /* the reference estimator exactly: adaptive early-out, r2 = 10*xi, roulette */
+       VMN_MODE_FIXED = 1 };  /* exact spp, r2 = xi, at most max_segments rays per path */
+
+typedef struct {
+    int32_t mode;           /* VMN_MODE_* */
+    uint32_t max_segments;  /* FIXED only; 0 = 5 (primary + 4 bounces) */
+    uint64_t seed;          /* Philox key */
+    uint64_t pixel_begin, pixel_end; /* pixel range [begin,end) this context renders; end = 0 -> width*height */
+    uint32_t sample_begin, sample_end; /* FIXED: sample slice [begin,end) of the spp-long sequence; end = 0 -> spp */
+    uint32_t tile_size;     /* 0 = contiguous pixel range; else pixel_begin/end index interleaved tiles (see vmn_render) */
+    uint32_t tile_rank, tile_world; /* tile t belongs to this context iff t % tile_world == tile_rank */
+    uint32_t reserved;
+} vmn_render_params;
+
+typedef struct {
+    uint64_t n_triangles, n_nodes, n_wide_nodes;
+    uint64_t node_bytes, tri_bytes;   /* bytes of one node / triangle record as laid out in HBM */
+    double build_ms;                  /* last vmn_scene_commit, device time */
+    uint64_t rays_traced;             /* extend-stage rays of the last render / intersect call */
+    uint64_t paths_traced;            /* samples finished by the last render */
+    uint64_t nodes_visited, tris_tested; /* only with VMN_CFG_COUNTERS */
+    double extend_ms, shade_ms, raygen_ms, resolve_ms, total_ms; /* device time of the last render, per stage */
+    uint64_t kernel_launches;         /* kernels launched by the last render / intersect call */
+} vmn_stats;
+
+/* lifetime (replaces `new PathTracer()` + RenderEngine::assignIntegrator, main.cpp:60-63) */
+int vmn_abi_version(void);
+vmn_status vmn_create(const vmn_config* cfg, vmn_ctx** out);
+void vmn_destroy(vmn_ctx* ctx);
+const char* vmn_last_error(const vmn_ctx* ctx);
+vmn_status vmn_set_stream(vmn_ctx* ctx, void* cuda_stream);
+vmn_status vmn_synchronize(vmn_ctx* ctx);
+
+/* scene (replaces MeshEngine::createBVH, meshEngine.cpp:649-724, and `new BVH(tris)`, bvh.cpp:155-279).
+ * pos: 9 floats per triangle; nrm: 9 per triangle or NULL (zeros); uv: 6 per triangle or NULL. */
+vmn_status vmn_scene_set_triangles(vmn_ctx* ctx, const float* pos, const float* nrm, const float* uv, uint64_t n);
+vmn_status vmn_scene_set_spheres(vmn_ctx* ctx, const vmn_sphere* spheres, uint32_t n); /* n <= 16; 0 disables */
+void vmn_reference_spheres(vmn_sphere out[8]); /* the eight spheres of meshEngine.cpp:377-500 */
+/* replaces MeshEngine::bindTexture's upload (meshEngine.cpp:85-91); slot 0 is the one Radiance samples */
+vmn_status vmn_scene_set_texture(vmn_ctx* ctx, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t c);
+vmn_status vmn_scene_commit(vmn_ctx* ctx); /* builds the BVH on the GPU */
+
+/* ray queries */
+#define VMN_ISECT_BVH2 1u /* traverse the binary LBVH instead of the compressed BVH8 (baseline / cross-check) */
+/* replaces BVH::getIntersection(ray, &info, false) (bvh.cpp:47-145) for n rays */
+vmn_status vmn_intersect(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, vmn_hit* out, uint32_t flags);
+vmn_status vmn_intersect_device(vmn_ctx* ctx, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags);
+/* replaces MeshEngine::RayCastCollision (meshEngine.cpp:196-207): out[i] = 1 iff closest hit has t > 1e-3 */
+vmn_status vmn_occluded(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, uint8_t* out);
+/* replaces MeshEngine::RayCast (meshEngine.cpp:239-509) for n rays */
+vmn_status vmn_raycast(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, vmn_raycast_rec* out);
+/* replaces Radiance() (pathtracer.cpp:21-198) for n start rays: Philox stream (seed, pixel = i, sample 0),
+ * draws start at index 2. out: 4 floats per ray; rays_cast (optional): RayCast count per path. */
+vmn_status vmn_radiance(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, uint64_t seed, int32_t mode, uint32_t max_segments,
+                        float* out, uint32_t* rays_cast);
+
+/* camera + film (replaces the Camera fields PathTracer::Render reads, camera.h:66-104) */
+vmn_status vmn_camera_set(vmn_ctx* ctx, const vmn_camera* cam);
+/* primary rays of pixel loop pathtracer.cpp:251-280 for given (pixel, stratum, jitter) tuples; parity helper */
+vmn_status vmn_camera_rays(vmn_ctx* ctx, const uint64_t* pixel, const uint32_t* sx, const uint32_t* sy, const float* jx,
+                           const float* jy, uint64_t n, vmn_ray* out);
+
+/* replaces PathTracer::Render's pixel loop (pathtracer.cpp:226-324) over this context's share of the frame */
+vmn_status vmn_render(vmn_ctx* ctx, const vmn_render_params* params);
+/* film readback. VMN_FILM_RGBAZ = Camera::mImage layout, 5 floats per pixel (camera.cpp:106-113): clamped rgb, alpha 1,
+ * depth = samples taken. VMN_FILM_SUM = raw (sum r, sum g, sum b, n) 4 floats per pixel (for sample-slice all-reduce). */
+enum { VMN_FILM_RGBAZ = 0, VMN_FILM_SUM = 1 };
+vmn_status vmn_read_image(vmn_ctx* ctx, float* dst, int32_t layout);
+/* device pointer to the raw sum buffer (4 floats per pixel, width*height pixels) for NCCL all-reduce / gather by the host */
+vmn_status vmn_film_device(vmn_ctx* ctx, float** d_sum, uint64_t* n_floats);
+/* resolve an (externally reduced) sum buffer already on the device into RGBAZ on the host */
+vmn_status vmn_film_resolve_device(vmn_ctx* ctx, const float* d_sum, float* dst_rgbaz);
+
+vmn_status vmn_get_stats(vmn_ctx* ctx, vmn_stats* out);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif

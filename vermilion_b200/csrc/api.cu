@@ -1,0 +1,404 @@
+// api.cu — the extern "C" surface of libvermilion_b200.so (include/vermilion_b200.h).
+#include "engine.cuh"
+
+#include <cstdarg>
+#include <cmath>
+#include <new>
+
+namespace vmn {
+
+vmn_status fail(vmn_ctx* c, vmn_status s, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return s;
+}
+
+void dev_free(DevBuf& b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.bytes = 0;
+}
+
+vmn_status dev_alloc(vmn_ctx* c, DevBuf& b, size_t bytes) {
+    dev_free(b);
+    if (bytes == 0) return VMN_OK;
+    cudaError_t e = cudaMalloc(&b.p, bytes);
+    if (e != cudaSuccess) {
+        b.p = nullptr;
+        cudaGetLastError();
+        return fail(c, e == cudaErrorMemoryAllocation ? VMN_ERR_OOM : VMN_ERR_CUDA, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+    }
+    b.bytes = bytes;
+    return VMN_OK;
+}
+
+vmn_status dev_reserve(vmn_ctx* c, DevBuf& b, size_t bytes) {
+    if (b.bytes >= bytes && b.p) return VMN_OK;
+    return dev_alloc(c, b, bytes);
+}
+
+// glm::rotate (extern/glm/glm/ext/matrix_transform.inl:18-46) composed as pathtracer.cpp:216-221, in host fp32.
+// Compiled by nvcc's host compiler without fast-math; column-major m[col*4+row].
+static void rotate(float m[16], float angle, float ax, float ay, float az) {
+    const float c = std::cos(angle), s = std::sin(angle);
+    const float inv = 1.0f / std::sqrt((ax * ax + ay * ay) + az * az);
+    const float x = ax * inv, y = ay * inv, z = az * inv;
+    const float tx = x * (1.f - c), ty = y * (1.f - c), tz = z * (1.f - c);
+    float R[3][3];
+    R[0][0] = c + tx * x; R[0][1] = tx * y + s * z; R[0][2] = tx * z - s * y;
+    R[1][0] = ty * x - s * z; R[1][1] = c + ty * y; R[1][2] = ty * z + s * x;
+    R[2][0] = tz * x + s * y; R[2][1] = tz * y - s * x; R[2][2] = c + tz * z;
+    float out[16];
+    for (int col = 0; col < 3; ++col)
+        for (int r = 0; r < 4; ++r) out[col * 4 + r] = m[0 * 4 + r] * R[col][0] + m[1 * 4 + r] * R[col][1] + m[2 * 4 + r] * R[col][2];
+    for (int r = 0; r < 4; ++r) out[12 + r] = m[12 + r];
+    memcpy(m, out, sizeof(out));
+}
+
+void camera_matrix(const vmn_camera& cam, float m[16]) {
+    for (int i = 0; i < 16; ++i) m[i] = (i % 5 == 0) ? 1.f : 0.f;
+    rotate(m, cam.rotation[1], 0, 1, 0);
+    rotate(m, cam.rotation[0], 1, 0, 0);
+    rotate(m, cam.rotation[2], 0, 0, 1);
+}
+
+} // namespace vmn
+
+using namespace vmn;
+
+#define CHECK_CTX(c) do { if (!(c)) return VMN_ERR_INVALID; } while (0)
+#define SET_DEVICE(c) VMN_CUDA(c, cudaSetDevice((c)->device))
+
+extern "C" {
+
+int vmn_abi_version(void) { return VMN_ABI_VERSION; }
+
+vmn_status vmn_create(const vmn_config* cfg, vmn_ctx** out) {
+    if (!out) return VMN_ERR_INVALID;
+    *out = nullptr;
+    vmn_ctx* c = new (std::nothrow) vmn_ctx();
+    if (!c) return VMN_ERR_OOM;
+    *out = c; // returned even on failure so that vmn_last_error can be read; caller still destroys it
+    c->device = cfg ? cfg->device : 0;
+    c->flags = cfg ? cfg->flags : 0;
+    c->max_paths = (cfg && cfg->max_paths) ? cfg->max_paths : (4ull << 20);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(c, VMN_ERR_CUDA, "no CUDA device (%s); this engine has no CPU fallback", e == cudaSuccess ? "count = 0" : cudaGetErrorString(e));
+    if (c->device < 0 || c->device >= ndev) return fail(c, VMN_ERR_INVALID, "device %d out of range [0,%d)", c->device, ndev);
+    SET_DEVICE(c);
+    cudaDeviceProp prop;
+    VMN_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
+    c->sm_count = prop.multiProcessorCount;
+    if (cfg && cfg->stream) { c->stream = (cudaStream_t)cfg->stream; c->own_stream = false; }
+    else { VMN_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
+    for (auto& ev : c->ev) VMN_CUDA(c, cudaEventCreate(&ev));
+    return VMN_OK;
+}
+
+void vmn_destroy(vmn_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    pool_destroy(c);
+    for (DevBuf* b : {&c->pos, &c->nrm, &c->uv, &c->tris, &c->tris_sorted, &c->tris_orig, &c->shade, &c->wide, &c->b_min, &c->b_max,
+                      &c->b_child, &c->spheres, &c->tex, &c->film, &c->q_in, &c->q_out, &c->counters})
+        dev_free(*b);
+    for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* vmn_last_error(const vmn_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+vmn_status vmn_set_stream(vmn_ctx* c, void* s) {
+    CHECK_CTX(c);
+    SET_DEVICE(c);
+    if (c->stream) VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->own_stream = false;
+    if (s) c->stream = (cudaStream_t)s;
+    else { VMN_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
+    return VMN_OK;
+}
+
+vmn_status vmn_synchronize(vmn_ctx* c) {
+    CHECK_CTX(c);
+    SET_DEVICE(c);
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VMN_OK;
+}
+
+static vmn_status upload(vmn_ctx* c, DevBuf& b, const void* src, size_t bytes) {
+    vmn_status s = dev_alloc(c, b, bytes);
+    if (s != VMN_OK) return s;
+    if (bytes) VMN_CUDA(c, cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    return VMN_OK;
+}
+
+vmn_status vmn_scene_set_triangles(vmn_ctx* c, const float* pos, const float* nrm, const float* uv, uint64_t n) {
+    CHECK_CTX(c);
+    if (n && !pos) return fail(c, VMN_ERR_INVALID, "pos is NULL");
+    SET_DEVICE(c);
+    c->committed = false;
+    c->n_tris = 0;
+    vmn_status s;
+    if ((s = upload(c, c->pos, pos, 36ull * n)) != VMN_OK) return s;
+    if (nrm) { if ((s = upload(c, c->nrm, nrm, 36ull * n)) != VMN_OK) return s; } else dev_free(c->nrm);
+    if (uv) { if ((s = upload(c, c->uv, uv, 24ull * n)) != VMN_OK) return s; } else dev_free(c->uv);
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // host pointers are borrowed for the call only
+    c->n_tris = n;
+    return VMN_OK;
+}
+
+vmn_status vmn_scene_set_spheres(vmn_ctx* c, const vmn_sphere* sp, uint32_t n) {
+    CHECK_CTX(c);
+    if (n > 16 || (n && !sp)) return fail(c, VMN_ERR_INVALID, "at most 16 spheres");
+    SET_DEVICE(c);
+    static_assert(sizeof(vmn_sphere) == sizeof(SphereDev), "sphere layouts must match");
+    vmn_status s = upload(c, c->spheres, sp, sizeof(vmn_sphere) * (size_t)n);
+    if (s != VMN_OK) return s;
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->n_spheres = n;
+    c->scene.n_spheres = n;
+    return VMN_OK;
+}
+
+void vmn_reference_spheres(vmn_sphere out[8]) {
+    memset(out, 0, sizeof(vmn_sphere) * 8);
+    auto set = [&](int i, float cx, float cy, float cz, float r, float ex, float ey, float ez, uint32_t flags, float nx, float ny, float nz) {
+        out[i].center[0] = cx; out[i].center[1] = cy; out[i].center[2] = cz; out[i].radius = r;
+        out[i].emission[0] = ex; out[i].emission[1] = ey; out[i].emission[2] = ez; out[i].flags = flags;
+        out[i].normal_center[0] = nx; out[i].normal_center[1] = ny; out[i].normal_center[2] = nz;
+    };
+    // meshEngine.cpp:377-387 and :410-420 — emitters; normals are measured from other points than the centres
+    set(0, 15.f, 140.f, 25.f, 3.5f, 0.f * 15.f, .5f * 15.f, 1.0f * 15.f, VMN_SPH_FLIP_NORMAL, -55.f, 350.f, -150.f);
+    set(1, 0.f, 3300.f, 1300.f, 250.f, 1.0f * 15.2f, 1.0f * 15.2f, 1.0f * 15.2f, 0u, 500.f, 800.f, 1300.f);
+    // meshEngine.cpp:424-500 — six radius-5e7 walls; centres computed in double, narrowed by the vec3 constructor
+    const double S = 1e7 * 5;
+    const float R = (float)S;
+    set(2, 0.f, (float)-S, 0.f, R, 0, 0, 0, 0u, 0.f, (float)-S, 0.f);
+    set(3, 0.f, (float)(S + 1000), 0.f, R, 0, 0, 0, 0u, 0.f, (float)(S + 1000), 0.f);
+    set(4, (float)(-S + 2000), 0.f, 0.f, R, 0, 0, 0, VMN_SPH_FLIP_NORMAL, (float)(-S + 2000), 0.f, 0.f);
+    set(5, (float)(S - 2000), 0.f, 0.f, R, 0, 0, 0, VMN_SPH_FLIP_NORMAL, (float)(S - 2000), 0.f, 0.f);
+    set(6, 0.f, 0.f, (float)(-S + 2000), R, 0, 0, 0, VMN_SPH_FLIP_NORMAL, 0.f, 0.f, (float)(-S + 2000));
+    set(7, 0.f, 0.f, (float)(S - 2000), R, 0, 0, 0, 0u, 0.f, 0.f, (float)(S - 2000));
+}
+
+vmn_status vmn_scene_set_texture(vmn_ctx* c, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t ch) {
+    CHECK_CTX(c);
+    if (slot != 0) return fail(c, VMN_ERR_INVALID, "only texture slot 0 is sampled (pathtracer.cpp:62-80)");
+    if (!data || !w || !h || ch < 1 || ch > 4) return fail(c, VMN_ERR_INVALID, "bad texture");
+    SET_DEVICE(c);
+    vmn_status s = upload(c, c->tex, data, sizeof(float) * (size_t)w * h * ch);
+    if (s != VMN_OK) return s;
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->tex_w = w; c->tex_h = h; c->tex_c = ch;
+    c->scene.tex = c->tex.as<float>(); c->scene.tex_w = w; c->scene.tex_h = h; c->scene.tex_c = ch;
+    return VMN_OK;
+}
+
+vmn_status vmn_scene_commit(vmn_ctx* c) {
+    CHECK_CTX(c);
+    SET_DEVICE(c);
+    vmn_status s = build_bvh(c);
+    if (s != VMN_OK) return s;
+    c->scene.n_spheres = c->n_spheres;
+    c->scene.tex = c->tex.as<float>(); c->scene.tex_w = c->tex_w; c->scene.tex_h = c->tex_h; c->scene.tex_c = c->tex_c;
+    // the staged host arrays are no longer needed
+    dev_free(c->pos); dev_free(c->nrm); dev_free(c->uv);
+    c->committed = true;
+    return VMN_OK;
+}
+
+} // extern "C"
+
+// ---- ray queries ----------------------------------------------------------------------------------
+#define NEED_COMMIT(c) do { if (!(c)->committed) return fail((c), VMN_ERR_STATE, "scene not committed (call vmn_scene_commit)"); } while (0)
+
+namespace {
+// stage host rays on the device in the context's scratch buffers
+vmn_status stage_rays(vmn_ctx* c, const vmn_ray* rays, uint64_t n, size_t out_bytes_per_ray) {
+    vmn_status s;
+    if ((s = dev_reserve(c, c->q_in, sizeof(vmn_ray) * n)) != VMN_OK) return s;
+    if ((s = dev_reserve(c, c->q_out, out_bytes_per_ray * n)) != VMN_OK) return s;
+    if (n) VMN_CUDA(c, cudaMemcpyAsync(c->q_in.p, rays, sizeof(vmn_ray) * n, cudaMemcpyHostToDevice, c->stream));
+    return VMN_OK;
+}
+vmn_status fetch(vmn_ctx* c, void* dst, size_t bytes) {
+    if (bytes) VMN_CUDA(c, cudaMemcpyAsync(dst, c->q_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VMN_OK;
+}
+vmn_status read_counters(vmn_ctx* c) {
+    if ((c->flags & VMN_CFG_COUNTERS) && c->counters.p) {
+        unsigned long long h[4] = {0, 0, 0, 0};
+        VMN_CUDA(c, cudaMemcpy(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost));
+        c->stats.nodes_visited = h[2]; c->stats.tris_tested = h[3];
+    }
+    return VMN_OK;
+}
+} // namespace
+
+extern "C" {
+
+vmn_status vmn_intersect_device(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (n && (!d_rays || !d_out)) return fail(c, VMN_ERR_INVALID, "null ray/hit pointer");
+    SET_DEVICE(c);
+    return launch_intersect(c, d_rays, n, d_out, flags);
+}
+
+vmn_status vmn_intersect(vmn_ctx* c, const vmn_ray* rays, uint64_t n, vmn_hit* out, uint32_t flags) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (n && (!rays || !out)) return fail(c, VMN_ERR_INVALID, "null ray/hit pointer");
+    SET_DEVICE(c);
+    vmn_status s;
+    if ((s = stage_rays(c, rays, n, sizeof(vmn_hit))) != VMN_OK) return s;
+    if ((s = launch_intersect(c, c->q_in.as<vmn_ray>(), n, c->q_out.as<vmn_hit>(), flags)) != VMN_OK) return s;
+    if ((s = fetch(c, out, sizeof(vmn_hit) * n)) != VMN_OK) return s;
+    if (n) { float ms = 0.f; cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->stats.extend_ms = ms; c->stats.total_ms = ms; }
+    return read_counters(c);
+}
+
+vmn_status vmn_occluded(vmn_ctx* c, const vmn_ray* rays, uint64_t n, uint8_t* out) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (n && (!rays || !out)) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    vmn_status s;
+    if ((s = stage_rays(c, rays, n, 1)) != VMN_OK) return s;
+    if ((s = launch_occluded(c, c->q_in.as<vmn_ray>(), n, c->q_out.as<uint8_t>())) != VMN_OK) return s;
+    return fetch(c, out, n);
+}
+
+vmn_status vmn_raycast(vmn_ctx* c, const vmn_ray* rays, uint64_t n, vmn_raycast_rec* out) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (n && (!rays || !out)) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    vmn_status s;
+    if ((s = stage_rays(c, rays, n, sizeof(vmn_raycast_rec))) != VMN_OK) return s;
+    if ((s = launch_raycast(c, c->q_in.as<vmn_ray>(), n, c->q_out.as<vmn_raycast_rec>())) != VMN_OK) return s;
+    return fetch(c, out, sizeof(vmn_raycast_rec) * n);
+}
+
+vmn_status vmn_radiance(vmn_ctx* c, const vmn_ray* rays, uint64_t n, uint64_t seed, int32_t mode, uint32_t max_segments, float* out,
+                        uint32_t* rays_cast) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (n && (!rays || !out)) return fail(c, VMN_ERR_INVALID, "null pointer");
+    if (mode != VMN_MODE_COMPAT && mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "bad mode %d", mode);
+    SET_DEVICE(c);
+    vmn_status s;
+    if ((s = stage_rays(c, rays, n, 16 + 4)) != VMN_OK) return s;
+    float* d_out = c->q_out.as<float>();
+    uint32_t* d_cnt = reinterpret_cast<uint32_t*>(d_out + 4 * n);
+    if ((s = launch_radiance(c, c->q_in.as<vmn_ray>(), n, seed, mode, max_segments ? max_segments : 5, d_out, d_cnt)) != VMN_OK) return s;
+    if (n) VMN_CUDA(c, cudaMemcpyAsync(out, d_out, 16 * n, cudaMemcpyDeviceToHost, c->stream));
+    if (n && rays_cast) VMN_CUDA(c, cudaMemcpyAsync(rays_cast, d_cnt, 4 * n, cudaMemcpyDeviceToHost, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VMN_OK;
+}
+
+// ---- camera, film, render -------------------------------------------------------------------------
+vmn_status vmn_camera_set(vmn_ctx* c, const vmn_camera* cam) {
+    CHECK_CTX(c);
+    if (!cam || !cam->width || !cam->height) return fail(c, VMN_ERR_INVALID, "bad camera");
+    SET_DEVICE(c);
+    c->cam = *cam;
+    camera_matrix(c->cam, c->cam_m);
+    c->have_cam = true;
+    const uint64_t npix = (uint64_t)cam->width * cam->height;
+    if (npix != c->film_pixels) {
+        vmn_status s = dev_alloc(c, c->film, 16 * npix);
+        if (s != VMN_OK) return s;
+        c->film_pixels = npix;
+    }
+    VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
+    return VMN_OK;
+}
+
+vmn_status vmn_camera_rays(vmn_ctx* c, const uint64_t* pixel, const uint32_t* sx, const uint32_t* sy, const float* jx, const float* jy,
+                           uint64_t n, vmn_ray* out) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (n && (!pixel || !sx || !sy || !jx || !jy || !out)) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    vmn_status s;
+    if ((s = dev_reserve(c, c->q_in, 24 * n)) != VMN_OK) return s;
+    if ((s = dev_reserve(c, c->q_out, sizeof(vmn_ray) * n)) != VMN_OK) return s;
+    char* base = c->q_in.as<char>();
+    uint64_t* d_px = reinterpret_cast<uint64_t*>(base);
+    uint32_t* d_sx = reinterpret_cast<uint32_t*>(base + 8 * n);
+    uint32_t* d_sy = d_sx + n;
+    float* d_jx = reinterpret_cast<float*>(d_sy + n);
+    float* d_jy = d_jx + n;
+    if (n) {
+        VMN_CUDA(c, cudaMemcpyAsync(d_px, pixel, 8 * n, cudaMemcpyHostToDevice, c->stream));
+        VMN_CUDA(c, cudaMemcpyAsync(d_sx, sx, 4 * n, cudaMemcpyHostToDevice, c->stream));
+        VMN_CUDA(c, cudaMemcpyAsync(d_sy, sy, 4 * n, cudaMemcpyHostToDevice, c->stream));
+        VMN_CUDA(c, cudaMemcpyAsync(d_jx, jx, 4 * n, cudaMemcpyHostToDevice, c->stream));
+        VMN_CUDA(c, cudaMemcpyAsync(d_jy, jy, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    }
+    if ((s = launch_camera_rays(c, d_px, d_sx, d_sy, d_jx, d_jy, n, c->q_out.as<vmn_ray>())) != VMN_OK) return s;
+    return fetch(c, out, sizeof(vmn_ray) * n);
+}
+
+vmn_status vmn_render(vmn_ctx* c, const vmn_render_params* p) {
+    CHECK_CTX(c);
+    NEED_COMMIT(c);
+    if (!p) return fail(c, VMN_ERR_INVALID, "null params");
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (p->mode != VMN_MODE_COMPAT && p->mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "bad mode %d", p->mode);
+    SET_DEVICE(c);
+    return render_frame(c, p);
+}
+
+vmn_status vmn_film_device(vmn_ctx* c, float** d_sum, uint64_t* n_floats) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (d_sum) *d_sum = c->film.as<float>();
+    if (n_floats) *n_floats = 4 * c->film_pixels;
+    return VMN_OK;
+}
+
+vmn_status vmn_film_resolve_device(vmn_ctx* c, const float* d_sum, float* dst) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (!d_sum || !dst) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    vmn_status s = dev_reserve(c, c->q_out, 20 * c->film_pixels);
+    if (s != VMN_OK) return s;
+    if ((s = film_resolve(c, d_sum, c->q_out.as<float>(), c->film_pixels)) != VMN_OK) return s;
+    return fetch(c, dst, 20 * c->film_pixels);
+}
+
+vmn_status vmn_read_image(vmn_ctx* c, float* dst, int32_t layout) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (!dst) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    if (layout == VMN_FILM_SUM) {
+        VMN_CUDA(c, cudaMemcpyAsync(dst, c->film.p, 16 * c->film_pixels, cudaMemcpyDeviceToHost, c->stream));
+        VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+        return VMN_OK;
+    }
+    if (layout != VMN_FILM_RGBAZ) return fail(c, VMN_ERR_INVALID, "bad layout %d", layout);
+    return vmn_film_resolve_device(c, c->film.as<float>(), dst);
+}
+
+vmn_status vmn_get_stats(vmn_ctx* c, vmn_stats* out) {
+    CHECK_CTX(c);
+    if (!out) return VMN_ERR_INVALID;
+    *out = c->stats;
+    return VMN_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,92 @@
+// engine.cuh — the context behind the C ABI (include/vermilion_b200.h) and the internal launch API.
+#pragma once
+#include "common.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace vmn {
+
+// device buffer owned by the context
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PathPool; // wavefront state (wavefront.cu)
+
+} // namespace vmn
+
+struct vmn_ctx {
+    int device = 0;
+    uint32_t flags = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = VMN_SM_COUNT_DEFAULT;
+    std::string err;
+
+    // host-provided scene, staged on the device until commit
+    vmn::DevBuf pos, nrm, uv;
+    uint64_t n_tris = 0;
+    bool committed = false;
+
+    // built scene
+    vmn::DevBuf tris, tris_sorted, tris_orig, shade, wide, b_min, b_max, b_child;
+    vmn::DevBuf spheres, tex;
+    uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0;
+    uint64_t n_wide = 0;
+    vmn::SceneDev scene{};
+
+    // camera / film
+    vmn_camera cam{};
+    bool have_cam = false;
+    float cam_m[16];
+    vmn::DevBuf film;      // float4 (sum r,g,b, n) per pixel
+    uint64_t film_pixels = 0;
+
+    // wavefront pool
+    uint64_t max_paths = 0;
+    vmn::PathPool* pool = nullptr;
+
+    // scratch for the ray-query entry points
+    vmn::DevBuf q_in, q_out, counters;
+
+    vmn_stats stats{};
+    cudaEvent_t ev[8] = {};
+};
+
+namespace vmn {
+
+vmn_status fail(vmn_ctx* c, vmn_status s, const char* fmt, ...);
+vmn_status dev_alloc(vmn_ctx* c, DevBuf& b, size_t bytes);       // (re)allocate exactly
+vmn_status dev_reserve(vmn_ctx* c, DevBuf& b, size_t bytes);     // grow only
+void dev_free(DevBuf& b);
+
+#define VMN_CUDA(c, expr)                                                                                   \
+    do {                                                                                                    \
+        cudaError_t e__ = (expr);                                                                           \
+        if (e__ != cudaSuccess) return vmn::fail((c), VMN_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__)); \
+    } while (0)
+
+// bvh_build.cu
+vmn_status build_bvh(vmn_ctx* c);
+
+// traverse.cu
+vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags);
+vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_t* d_out);
+vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_raycast_rec* d_out);
+
+// wavefront.cu
+vmn_status launch_radiance(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint64_t seed, int mode, uint32_t max_segments,
+                           float* d_out, uint32_t* d_rays_cast);
+vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_t* d_sx, const uint32_t* d_sy, const float* d_jx,
+                              const float* d_jy, uint64_t n, vmn_ray* d_out);
+vmn_status render_frame(vmn_ctx* c, const vmn_render_params* p);
+vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix);
+void pool_destroy(vmn_ctx* c);
+void camera_matrix(const vmn_camera& cam, float m[16]);
+
+} // namespace vmn

@@ -1,0 +1,161 @@
+// traverse.cu — ray-query kernels behind vmn_intersect / vmn_occluded / vmn_raycast.
+//
+// Persistent warps: the grid is sized to (SM count x resident blocks per SM); each warp claims 32
+// consecutive rays at a time with one atomicAdd (lane 0) + shuffle, so long rays do not leave a
+// tail of idle blocks. The BVH8 traversal stack lives in shared memory, strided so that the 32
+// lanes of a warp hit 32 different banks pairs (uint2 entries, conflict-free 64-bit accesses).
+#include "engine.cuh"
+#include "traverse.cuh"
+
+namespace vmn {
+
+constexpr int kTraceBlock = 128;
+
+__device__ __forceinline__ bool claim_rays(unsigned long long* next, uint64_t n, uint64_t* i_out) {
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(next, 32ull);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) return false;
+    *i_out = base + (threadIdx.x & 31);
+    return true;
+}
+
+__device__ __forceinline__ void load_ray(const vmn_ray* __restrict__ rays, uint64_t i, V3* o, V3* d) {
+    const float4* p = reinterpret_cast<const float4*>(rays + i);
+    const float4 a = __ldg(p), b = __ldg(p + 1);
+    *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
+}
+
+// closest hit; returns original triangle id (or VMN_MISS) and t
+template <bool WIDE, bool COUNT>
+__device__ __forceinline__ uint32_t closest_hit(const SceneDev& sc, V3 o, V3 d, float* t, uint2* sstack, TravCounters* cnt) {
+    uint32_t k;
+    const TriRec* base;
+    if (WIDE) { k = trace_wide<COUNT>(sc, o, d, t, sstack, kTraceBlock, cnt); base = sc.tris; }
+    else { k = trace_bvh2<COUNT>(sc, o, d, t, cnt); base = sc.tris_sorted; }
+    if (k == VMN_MISS) return VMN_MISS;
+    return __float_as_uint(__ldg(&reinterpret_cast<const float4*>(base + k)->w));
+}
+
+template <bool WIDE, bool COUNT>
+__global__ void __launch_bounds__(kTraceBlock) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
+                                                           vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    TravCounters cnt{0ull, 0ull};
+    uint64_t i;
+    while (claim_rays(next, n, &i)) {
+        if (i >= n) continue;
+        V3 o, d;
+        load_ray(rays, i, &o, &d);
+        float t;
+        const uint32_t id = closest_hit<WIDE, COUNT>(sc, o, d, &t, sstack, &cnt);
+        float u = 0.f, v = 0.f;
+        if (id != VMN_MISS) {
+            const V3 hp = o + d * t; // bvh.cpp:140
+            tri_bary(load_tri(sc.tris_orig + id), hp, &u, &v);
+        }
+        reinterpret_cast<float4*>(out)[i] = make_float4(t, u, v, __uint_as_float(id));
+    }
+    if (COUNT) {
+        atomicAdd(&gcnt->nodes, cnt.nodes);
+        atomicAdd(&gcnt->tris, cnt.tris);
+    }
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_occluded(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n, uint8_t* __restrict__ out,
+                                                          unsigned long long* next) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    uint64_t i;
+    while (claim_rays(next, n, &i)) {
+        if (i >= n) continue;
+        V3 o, d;
+        load_ray(rays, i, &o, &d);
+        float t;
+        const uint32_t id = closest_hit<true, false>(sc, o, d, &t, sstack, nullptr);
+        out[i] = (id != VMN_MISS && (double)t > 1e-3) ? 1 : 0; // meshEngine.cpp:196-207
+    }
+}
+
+__global__ void __launch_bounds__(kTraceBlock) k_raycast(SceneDev sc, const SphereDev* __restrict__ sph, const vmn_ray* __restrict__ rays, uint64_t n,
+                                                         vmn_raycast_rec* __restrict__ out, unsigned long long* next) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    uint64_t i;
+    while (claim_rays(next, n, &i)) {
+        if (i >= n) continue;
+        V3 o, d;
+        load_ray(rays, i, &o, &d);
+        float t;
+        const uint32_t id = closest_hit<true, false>(sc, o, d, &t, sstack, nullptr);
+        const RayCastOut r = raycast_finish(sc, sph, o, d, t, id);
+        float4* q = reinterpret_cast<float4*>(out + i);
+        q[0] = make_float4(r.P.x, r.P.y, r.P.z, r.dist);
+        q[1] = make_float4(r.N.x, r.N.y, r.N.z, __uint_as_float((r.hit ? VMN_RC_HIT : 0u) | (r.material ? VMN_RC_MATERIAL : 0u)));
+        q[2] = make_float4(r.uv0, r.uv1, r.Le.x, r.Le.y);
+        q[3] = make_float4(r.Le.z, __uint_as_float(r.tri), 0.f, 0.f);
+    }
+}
+
+template <class K>
+static int resident_grid(vmn_ctx* c, K kernel) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceBlock, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+    return c->sm_count * per_sm;
+}
+
+static vmn_status reset_counters(vmn_ctx* c) {
+    vmn_status s = dev_reserve(c, c->counters, 64);
+    if (s != VMN_OK) return s;
+    VMN_CUDA(c, cudaMemsetAsync(c->counters.p, 0, 64, c->stream));
+    return VMN_OK;
+}
+
+vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags) {
+    vmn_status s = reset_counters(c);
+    if (s != VMN_OK) return s;
+    auto* next = c->counters.as<unsigned long long>();
+    auto* gcnt = reinterpret_cast<TravCounters*>(c->counters.as<unsigned long long>() + 2);
+    const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
+    const bool wide = !(flags & VMN_ISECT_BVH2);
+    c->stats.kernel_launches = 0;
+    if (n) {
+        VMN_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+#define LAUNCH(W, C)                                                                                                           \
+    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt)
+        if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
+        else { if (count) LAUNCH(false, true); else LAUNCH(false, false); }
+#undef LAUNCH
+        VMN_CUDA(c, cudaGetLastError());
+        VMN_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+        c->stats.kernel_launches = 1;
+    }
+    c->stats.rays_traced = n;
+    return VMN_OK;
+}
+
+vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_t* d_out) {
+    vmn_status s = reset_counters(c);
+    if (s != VMN_OK) return s;
+    if (n) {
+        k_occluded<<<resident_grid(c, k_occluded), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, c->counters.as<unsigned long long>());
+        VMN_CUDA(c, cudaGetLastError());
+    }
+    c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;
+    return VMN_OK;
+}
+
+vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_raycast_rec* d_out) {
+    vmn_status s = reset_counters(c);
+    if (s != VMN_OK) return s;
+    if (n) {
+        k_raycast<<<resident_grid(c, k_raycast), kTraceBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), d_rays, n, d_out,
+                                                                            c->counters.as<unsigned long long>());
+        VMN_CUDA(c, cudaGetLastError());
+    }
+    c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;
+    return VMN_OK;
+}
+
+} // namespace vmn

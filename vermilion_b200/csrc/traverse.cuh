@@ -1,0 +1,270 @@
+// traverse.cuh — device-side closest-hit traversal and the RayCast restatement.
+//
+// Replaces, per ray: BVH::getIntersection (reference core/accelerators/bvh.cpp:47-145),
+// BBox::intersect (bbox.cpp:70-83), Triangle::getIntersection (triangle.cpp:4-54),
+// Triangle::getNormal (triangle.cpp:56-87), sphereIntersect and MeshEngine::RayCast
+// (core/engines/meshEngine.cpp:182-194, 239-509).
+//
+// Parity rules: the triangle test and everything that produces an OUTPUT value (t, barycentrics,
+// normals, sphere solves) uses the reference's exact fp32/fp64 operation order with no FMA
+// contraction (file is compiled -fmad=false). Box tests only have to be conservative, so they use
+// FMAs on the quantised boxes. Ties (equal t) keep the first triangle visited, as bvh.cpp:90 does;
+// the visiting order differs from the reference's tree, so exact ties may resolve differently.
+#pragma once
+#include "common.cuh"
+
+namespace vmn {
+
+#define VMN_T_MISS 999999999.f // bvh.cpp:48
+#define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
+#define VMN_LOCAL_STACK 52     // overflow entries in local memory
+
+struct TravCounters { unsigned long long nodes, tris; };
+
+// Triangle::getIntersection (triangle.cpp:4-54): Moeller-Trumbore, two-sided.
+__device__ __forceinline__ bool tri_intersect(const TriRec& T, V3 o, V3 d, float* t) {
+    V3 v0(T.r0.x, T.r0.y, T.r0.z), e1(T.r1.x, T.r1.y, T.r1.z), e2(T.r2.x, T.r2.y, T.r2.z);
+    V3 pvec = cross(d, e2);
+    float det = dot(e1, pvec);
+    if ((double)det < 1e-8 && (double)det > -1e-8) return false; // :25, compared as double
+    float inv_det = 1 / det;
+    V3 tvec = o - v0;
+    float u = dot(tvec, pvec) * inv_det;
+    if (u < 0 || u > 1) return false;
+    V3 qvec = cross(tvec, e1);
+    float v = dot(d, qvec) * inv_det;
+    if (v < 0 || u + v > 1) return false;
+    float dist = dot(e2, qvec) * inv_det;
+    if (dist > 0.0f) { *t = dist; return true; }
+    return false;
+}
+
+__device__ __forceinline__ TriRec load_tri(const TriRec* __restrict__ p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+    TriRec t; t.r0 = __ldg(q); t.r1 = __ldg(q + 1); t.r2 = __ldg(q + 2);
+    return t;
+}
+
+__device__ __forceinline__ bool ray_is_nan(V3 o, V3 d) {
+    return !(o.x == o.x && o.y == o.y && o.z == o.z && d.x == d.x && d.y == d.y && d.z == d.z);
+}
+
+__device__ __forceinline__ float safe_inv(float x) {
+    const float eps = 1e-20f;
+    return 1.0f / (fabsf(x) > eps ? x : copysignf(eps, x));
+}
+
+// ---- compressed BVH8 closest hit --------------------------------------------------------------
+// sstack: this thread's slice of the shared-memory stack, entries `sstride` uint2 apart.
+// Returns the index into sc.tris of the closest triangle (or VMN_MISS) and its t.
+template <bool COUNT>
+__device__ __forceinline__ uint32_t trace_wide(const SceneDev& sc, V3 o, V3 d, float* t_out, uint2* sstack, uint32_t sstride,
+                                               TravCounters* cnt) {
+    float best_t = VMN_T_MISS;
+    uint32_t best = VMN_MISS;
+    if (sc.n_tris == 0 || ray_is_nan(o, d)) { *t_out = best_t; return best; }
+    const float idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
+    const uint32_t oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
+    uint2 lstack[VMN_LOCAL_STACK];
+    int sp = 0;
+    uint2 ng = make_uint2(0u, 0x80000000u); // root: one pending hit at bit 31, imask 0
+    uint2 tg = make_uint2(0u, 0u);
+    const uint4* __restrict__ nodes = reinterpret_cast<const uint4*>(sc.nodes);
+
+    while (true) {
+        if (ng.y & 0xFF000000u) {
+            const uint32_t bit = 31u - __clz(ng.y);
+            const uint32_t slot = (bit - 24u) ^ oct_inv;
+            ng.y &= ~(1u << bit);
+            const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
+            const uint32_t nidx = ng.x + rel;
+            if (ng.y & 0xFF000000u) { // siblings still pending
+                if (sp < VMN_SH_STACK) sstack[sp * sstride] = ng; else lstack[sp - VMN_SH_STACK] = ng;
+                ++sp;
+            }
+            const uint4* np = nodes + 5ull * nidx;
+            const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
+            if (COUNT) ++cnt->nodes;
+            const float ax = __uint_as_float((q0.w & 0xFFu) << 23) * idx;
+            const float ay = __uint_as_float(((q0.w >> 8) & 0xFFu) << 23) * idy;
+            const float az = __uint_as_float(((q0.w >> 16) & 0xFFu) << 23) * idz;
+            const float bx = (__uint_as_float(q0.x) - o.x) * idx;
+            const float by = (__uint_as_float(q0.y) - o.y) * idy;
+            const float bz = (__uint_as_float(q0.z) - o.z) * idz;
+            // near/far byte planes per axis (two words = 8 children each)
+            uint32_t nx[2], fx[2], ny[2], fy[2], nz[2], fz[2];
+            if (d.x < 0.f) { nx[0] = q3.z; nx[1] = q3.w; fx[0] = q2.x; fx[1] = q2.y; } else { nx[0] = q2.x; nx[1] = q2.y; fx[0] = q3.z; fx[1] = q3.w; }
+            if (d.y < 0.f) { ny[0] = q4.x; ny[1] = q4.y; fy[0] = q2.z; fy[1] = q2.w; } else { ny[0] = q2.z; ny[1] = q2.w; fy[0] = q4.x; fy[1] = q4.y; }
+            if (d.z < 0.f) { nz[0] = q4.z; nz[1] = q4.w; fz[0] = q3.x; fz[1] = q3.y; } else { nz[0] = q3.x; nz[1] = q3.y; fz[0] = q4.z; fz[1] = q4.w; }
+            const uint32_t meta[2] = {q1.z, q1.w};
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t sh = 8u * j;
+                    const uint32_t m = (meta[h] >> sh) & 0xFFu;
+                    const float tnx = __fmaf_rn((float)((nx[h] >> sh) & 0xFFu), ax, bx);
+                    const float tny = __fmaf_rn((float)((ny[h] >> sh) & 0xFFu), ay, by);
+                    const float tnz = __fmaf_rn((float)((nz[h] >> sh) & 0xFFu), az, bz);
+                    const float tfx = __fmaf_rn((float)((fx[h] >> sh) & 0xFFu), ax, bx);
+                    const float tfy = __fmaf_rn((float)((fy[h] >> sh) & 0xFFu), ay, by);
+                    const float tfz = __fmaf_rn((float)((fz[h] >> sh) & 0xFFu), az, bz);
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
+                    if (tn <= tf) {
+                        const uint32_t inner = ((m & 0x18u) == 0x18u) ? 7u : 0u;
+                        const uint32_t bitidx = (m ^ (oct_inv & inner)) & 0x1Fu;
+                        hitmask |= (m >> 5) << bitidx;
+                    }
+                }
+            }
+            ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
+            tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
+        } else {
+            tg = ng;
+            ng = make_uint2(0u, 0u);
+        }
+        while (tg.y) {
+            const uint32_t i = __ffs(tg.y) - 1u;
+            tg.y &= tg.y - 1u;
+            const uint32_t ti = tg.x + i;
+            const TriRec T = load_tri(sc.tris + ti);
+            if (COUNT) ++cnt->tris;
+            float ct;
+            if (tri_intersect(T, o, d, &ct) && ct < best_t) { best_t = ct; best = ti; }
+        }
+        if ((ng.y & 0xFF000000u) == 0u) {
+            if (sp == 0) break;
+            --sp;
+            ng = (sp < VMN_SH_STACK) ? sstack[sp * sstride] : lstack[sp - VMN_SH_STACK];
+        }
+    }
+    *t_out = best_t;
+    return best;
+}
+
+// ---- binary LBVH closest hit (baseline / cross-check; stack in local memory) --------------------
+template <bool COUNT>
+__device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, float* t_out, TravCounters* cnt) {
+    float best_t = VMN_T_MISS;
+    uint32_t best = VMN_MISS; // index into sc.tris_sorted
+    const uint32_t n = sc.bvh2.n_prims;
+    if (n == 0 || ray_is_nan(o, d)) { *t_out = best_t; return best; }
+    const int nint = (int)n - 1;
+    const float idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
+    int stack[64];
+    int sp = 0;
+    int node = 0;
+    while (true) {
+        if (node >= nint) {
+            const uint32_t k = (uint32_t)(node - nint);
+            const TriRec T = load_tri(sc.tris_sorted + k);
+            if (COUNT) ++cnt->tris;
+            float ct;
+            if (tri_intersect(T, o, d, &ct) && ct < best_t) { best_t = ct; best = k; }
+            if (sp == 0) break;
+            node = stack[--sp];
+            continue;
+        }
+        if (COUNT) ++cnt->nodes;
+        const int2 c = __ldg(&sc.bvh2.child[node]);
+        float tn[2]; bool hit[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int ci = k ? c.y : c.x;
+            const float4 lo = __ldg(&sc.bvh2.bmin[ci]), hi = __ldg(&sc.bvh2.bmax[ci]);
+            const float x0 = (lo.x - o.x) * idx, x1 = (hi.x - o.x) * idx;
+            const float y0 = (lo.y - o.y) * idy, y1 = (hi.y - o.y) * idy;
+            const float z0 = (lo.z - o.z) * idz, z1 = (hi.z - o.z) * idz;
+            const float a = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.f));
+            const float b = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best_t));
+            // widen by a few ulp so that rounding in the slab products cannot reject a box the exact test accepts
+            hit[k] = a * 0.9999995f <= b * 1.0000005f;
+            tn[k] = a;
+        }
+        if (hit[0] && hit[1]) {
+            const bool swap = tn[1] < tn[0];
+            const int nearc = swap ? c.y : c.x, farc = swap ? c.x : c.y;
+            if (sp < 64) stack[sp++] = farc;
+            node = nearc;
+        } else if (hit[0]) node = c.x;
+        else if (hit[1]) node = c.y;
+        else {
+            if (sp == 0) break;
+            node = stack[--sp];
+        }
+    }
+    *t_out = best_t;
+    return best;
+}
+
+// Barycentric weights (w1, w2) of Triangle::getNormal (triangle.cpp:67-78) for hit point hp.
+__device__ __forceinline__ void tri_bary(const TriRec& T, V3 hp, float* w1, float* w2) {
+    V3 f0(T.r1.x, T.r1.y, T.r1.z), f1(T.r2.x, T.r2.y, T.r2.z);
+    V3 f2 = hp - V3(T.r0.x, T.r0.y, T.r0.z);
+    float d00 = dot(f0, f0), d01 = dot(f0, f1), d11 = dot(f1, f1), d20 = dot(f2, f0), d21 = dot(f2, f1);
+    float denom = d00 * d11 - d01 * d01;
+    *w1 = (d11 * d20 - d01 * d21) / denom;
+    *w2 = (d00 * d21 - d01 * d20) / denom;
+}
+
+// sphereIntersect (meshEngine.cpp:182-194): fp32 operands, fp64 solve, eps 1e-4.
+__device__ __forceinline__ float sphere_intersect(V3 pos, V3 rot, V3 p, const float rad) {
+    V3 op = p - pos;
+    double t;
+    const double eps = 1e-4;
+    double b = (double)dot(op, rot);
+    double det = b * b - (double)dot(op, op) + (double)(rad * rad);
+    if (det < 0) return 0;
+    det = sqrt(det);
+    return (float)((t = b - det) > eps ? t : ((t = b + det) > eps ? t : 0));
+}
+
+struct RayCastOut {
+    bool hit, material;
+    V3 P, N, Le;
+    float dist;
+    float uv0, uv1;
+    uint32_t tri;
+};
+
+// Everything MeshEngine::RayCast does after the BVH query (meshEngine.cpp:364-508).
+// bvh_t / tri_id: closest BVH hit (original triangle id or VMN_MISS).
+__device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const SphereDev* __restrict__ sph, V3 o, V3 d, float bvh_t,
+                                                     uint32_t tri_id) {
+    RayCastOut r;
+    r.N = V3(0, 0, 0); r.Le = V3(0, 0, 0); r.uv0 = 0.f; r.uv1 = 0.f; r.tri = tri_id;
+    float nearest = INFINITY;
+    r.material = tri_id != VMN_MISS;
+    if (r.material) {
+        nearest = bvh_t;
+        V3 hp = o + d * bvh_t; // bvh.cpp:140
+        const TriRec T = load_tri(sc.tris_orig + tri_id);
+        float w1, w2;
+        tri_bary(T, hp, &w1, &w2);
+        float w0 = 1 - w1 - w2;
+        const float4* sp4 = reinterpret_cast<const float4*>(sc.shade + tri_id);
+        const float4 s0 = __ldg(sp4), s1 = __ldg(sp4 + 1), s2 = __ldg(sp4 + 2), s3 = __ldg(sp4 + 3);
+        V3 n = V3(s0.x, s0.y, s0.z) * w0 + V3(s1.x, s1.y, s1.z) * w1 + V3(s2.x, s2.y, s2.z) * w2; // triangle.cpp:80
+        r.uv0 = s0.w * w0 + s2.w * w1 + s3.y * w2; // uv0.x, uv1.x, uv2.x  (triangle.cpp:83)
+        r.uv1 = s1.w * w0 + s3.x * w1 + s3.z * w2; // uv0.y, uv1.y, uv2.y
+        r.N = normalize(-n);                        // triangle.cpp:86, meshEngine.cpp:369
+    }
+    for (uint32_t i = 0; i < sc.n_spheres; ++i) { // meshEngine.cpp:377-500, fixed order, 0 < ts < nearest
+        const SphereDev s = sph[i];
+        float th = sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r);
+        if (th > 0.f && th < nearest) {
+            nearest = th;
+            if (s.ex != 0.f || s.ey != 0.f || s.ez != 0.f) r.Le = V3(s.ex, s.ey, s.ez);
+            V3 nn = normalize(o + (d * nearest) - V3(s.nx, s.ny, s.nz));
+            r.N = (s.flags & VMN_SPH_FLIP_NORMAL) ? -nn : nn;
+        }
+    }
+    r.P = o + (d * nearest);
+    r.dist = nearest;
+    r.hit = nearest < INFINITY;
+    return r;
+}
+
+} // namespace vmn

@@ -1,0 +1,636 @@
+// wavefront.cu — the path-tracing wavefront: raygen -> (extend -> shade)* -> accumulate -> resolve.
+//
+// Replaces PathTracer::Render's pixel loop and Radiance() (reference core/integrators/pathtracer.cpp:
+// 21-198, 200-328). Stages are separate kernels connected by device-resident ray queues:
+//   k_raygen      one thread per (pixel, sample) of the round: camera ray (pathtracer.cpp:251-280), path state reset
+//   k_extend      persistent warps, BVH8 closest hit per queued ray -> (t, triangle id)      [the hot kernel]
+//   k_shade       the rest of MeshEngine::RayCast (normals, 8 spheres) + one Radiance iteration; survivors are
+//                 appended to the next queue with one atomicAdd per warp (ballot/popc compaction)
+//   k_accumulate  per pixel, adds the round's finished samples to the film in sample order (deterministic,
+//                 no float atomics); in COMPAT mode also runs the reference's adaptive early-out state machine
+//   k_resolve     film sums -> RGBAZ (pathtracer.cpp:318-323, camera.cpp:106-113)
+// Path state is SoA indexed by slot; queue entries carry the slot. Queue counters live in device memory, so a
+// FIXED-mode round needs no host synchronisation.
+#include "engine.cuh"
+#include "traverse.cuh"
+
+namespace vmn {
+
+constexpr int kWfBlock = 128;
+
+// which pixels this context renders: a contiguous range or interleaved square tiles
+struct PixelMap {
+    uint32_t width, height;
+    uint64_t begin;       // contiguous: first pixel
+    uint32_t tile, rank, world, tiles_x;
+};
+
+__device__ __forceinline__ bool map_pixel(const PixelMap& m, uint64_t lp, uint64_t* pixel) {
+    if (m.tile == 0) { *pixel = m.begin + lp; return *pixel < (uint64_t)m.width * m.height; }
+    const uint32_t tt = m.tile * m.tile;
+    const uint64_t j = lp / tt;
+    const uint32_t w = (uint32_t)(lp % tt);
+    const uint64_t t = j * m.world + m.rank;
+    const uint32_t ty = (uint32_t)(t / m.tiles_x), tx = (uint32_t)(t % m.tiles_x);
+    const uint32_t x = tx * m.tile + (w % m.tile), y = ty * m.tile + (w / m.tile);
+    if (x >= m.width || y >= m.height) return false;
+    *pixel = (uint64_t)y * m.width + x;
+    return true;
+}
+
+struct CamDev {
+    float m[16];
+    float px, py, pz;
+    float dist, sx, sy;
+    uint32_t width, height, spp;
+};
+
+// pathtracer.cpp:251-280 (types follow the C++ promotions: the 0.25 / 0.5 literals are double)
+__device__ __forceinline__ void camera_ray(const CamDev& c, uint64_t p, uint32_t sampleX, uint32_t sampleY, float jx, float jy, V3* o, V3* d) {
+    float hx = (float)((((double)(float(p % c.width) + (sampleX * 0.5f - 0.5f) + jx) - 0.25) / (double)c.width) - 0.5);
+    float hy = (float)((((double)(float(p / c.width) + (sampleY * 0.5f - 0.5f) + jy) - 0.25) / (double)c.height) - 0.5);
+    float bx = hx * c.sx, by = hy * c.sy;
+    float g0 = bx, g1 = -by, g2 = -c.dist, g3 = 1.0f;
+    float rd[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) rd[r] = (c.m[r] * g0 + c.m[4 + r] * g1) + (c.m[8 + r] * g2 + c.m[12 + r] * g3);
+    V3 dir(rd[0] / rd[3], rd[1] / rd[3], rd[2] / rd[3]);
+    *d = normalize(dir);
+    *o = V3(c.px, c.py, c.pz);
+}
+
+struct PathPool {
+    uint64_t capacity = 0;
+    DevBuf ray[2];    // 32 B per entry: (o.xyz, slot) (d.xyz, 0)
+    DevBuf hit;       // float2 per queue entry: (t, original triangle id)
+    DevBuf radiance;  // float4 per slot (rgb, first-hit distance / -100)
+    DevBuf thr;       // float4 per slot
+    DevBuf meta;      // uint2 per slot: (draw counter, depth | segs<<16)
+    DevBuf ctl;       // uint32 counters: [0..1] queue counts, [8..] claim counters (unsigned long long)
+    DevBuf cstate;    // COMPAT per-local-pixel stratum state
+    uint32_t* h_count = nullptr; // pinned
+    std::vector<cudaEvent_t> events;
+    size_t ev_used = 0;
+};
+
+void pool_destroy(vmn_ctx* c) {
+    PathPool* p = c->pool;
+    if (!p) return;
+    for (DevBuf* b : {&p->ray[0], &p->ray[1], &p->hit, &p->radiance, &p->thr, &p->meta, &p->ctl, &p->cstate}) dev_free(*b);
+    if (p->h_count) cudaFreeHost(p->h_count);
+    for (auto e : p->events) cudaEventDestroy(e);
+    delete p;
+    c->pool = nullptr;
+}
+
+static vmn_status pool_ensure(vmn_ctx* c, uint64_t paths) {
+    if (!c->pool) c->pool = new PathPool();
+    PathPool* p = c->pool;
+    vmn_status s;
+    if (paths > p->capacity) {
+        if ((s = dev_alloc(c, p->ray[0], 32 * paths)) != VMN_OK) return s;
+        if ((s = dev_alloc(c, p->ray[1], 32 * paths)) != VMN_OK) return s;
+        if ((s = dev_alloc(c, p->hit, 8 * paths)) != VMN_OK) return s;
+        if ((s = dev_alloc(c, p->radiance, 16 * paths)) != VMN_OK) return s;
+        if ((s = dev_alloc(c, p->thr, 16 * paths)) != VMN_OK) return s;
+        if ((s = dev_alloc(c, p->meta, 8 * paths)) != VMN_OK) return s;
+        p->capacity = paths;
+    }
+    if (!p->ctl.p && (s = dev_alloc(c, p->ctl, 4096)) != VMN_OK) return s;
+    if (!p->h_count) VMN_CUDA(c, cudaMallocHost(&p->h_count, 64));
+    return VMN_OK;
+}
+
+// ---- raygen ----------------------------------------------------------------------------------------
+struct RoundParams {
+    uint64_t seed;
+    uint64_t n_local;   // local pixels in this chunk
+    uint64_t lp0;       // first local pixel of the chunk
+    uint32_t s0, batch; // first sample index, samples per pixel this round
+    uint32_t per;       // spp / 4 (stratum length)
+    int32_t mode;
+    uint32_t max_segments;
+};
+
+__global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, RoundParams rp, const uint32_t* __restrict__ cstate,
+                                                     float4* __restrict__ rays, uint32_t* __restrict__ qcount, float4* __restrict__ radiance,
+                                                     float4* __restrict__ thr, uint2* __restrict__ meta) {
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t total = rp.n_local * rp.batch;
+    bool live = idx < total;
+    uint64_t pixel = 0;
+    uint32_t sample = 0, sxy = 0;
+    if (live) {
+        const uint64_t lp = idx % rp.n_local;
+        const uint32_t k = (uint32_t)(idx / rp.n_local);
+        sample = rp.s0 + k;
+        live = map_pixel(pm, rp.lp0 + lp, &pixel);
+        if (live) {
+            if (rp.mode == VMN_MODE_COMPAT) {
+                const uint32_t st = cstate[lp] >> 30; // stratum 0..3, 4 (encoded as done flag below) never reaches here
+                live = (cstate[lp] & 0x20000000u) == 0u;
+                sxy = st;
+            } else {
+                sxy = rp.per ? ((sample / rp.per) & 3u) : 0u; // sampleX = bit 1, sampleY = bit 0 (loop nesting of pathtracer.cpp:242-247)
+            }
+        }
+        // every slot of the round gets a defined state, live or not
+        radiance[idx] = make_float4(0.f, 0.f, 0.f, live ? -100.f : 0.f);
+        thr[idx] = make_float4(1.f, 1.f, 1.f, 1.f);
+        meta[idx] = make_uint2(2u, live ? 0u : 0xFFFFFFFFu);
+    }
+    V3 o(0, 0, 0), d(0, 0, 0);
+    if (live) {
+        Rng rng(rp.seed, pixel, sample, 0);
+        const float jx = rng.jitter(), jy = rng.jitter();
+        camera_ray(cam, pixel, (sxy >> 1) & 1u, sxy & 1u, jx, jy, &o, &d);
+    }
+    // warp-aggregated append
+    const uint32_t ballot = __ballot_sync(0xffffffffu, live);
+    if (ballot == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == (uint32_t)(__ffs(ballot) - 1)) base = atomicAdd(qcount, (uint32_t)__popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
+    if (live) {
+        const uint32_t q = base + __popc(ballot & ((1u << lane) - 1u));
+        rays[2ull * q] = make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx));
+        rays[2ull * q + 1] = make_float4(d.x, d.y, d.z, 0.f);
+    }
+}
+
+// ---- extend ----------------------------------------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(kWfBlock) k_extend(SceneDev sc, const float4* __restrict__ rays, const uint32_t* __restrict__ qcount,
+                                                     float2* __restrict__ hits, unsigned long long* next, TravCounters* gcnt,
+                                                     unsigned long long* total_rays) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    const uint64_t n = *qcount;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total_rays, (unsigned long long)n);
+    TravCounters cnt{0ull, 0ull};
+    while (true) {
+        unsigned long long base = 0;
+        if ((threadIdx.x & 31) == 0) base = atomicAdd(next, 32ull);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint64_t i = base + (threadIdx.x & 31);
+        if (i >= n) continue;
+        const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
+        float t;
+        const uint32_t k = trace_wide<COUNT>(sc, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), &t, sstack, kWfBlock, &cnt);
+        uint32_t id = VMN_MISS;
+        if (k != VMN_MISS) id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + k)->w));
+        hits[i] = make_float2(t, __uint_as_float(id));
+    }
+    if (COUNT) { atomicAdd(&gcnt->nodes, cnt.nodes); atomicAdd(&gcnt->tris, cnt.tris); }
+}
+
+// ---- shade -----------------------------------------------------------------------------------------
+// VermiTexture::Sample (meshEngine.cpp:21-46)
+__device__ __forceinline__ void texture_sample(const SceneDev& sc, float u, float v, float out[4]) {
+    float sx = u - floorf(u), sy = v - floorf(v);
+    uint32_t mx = (uint32_t)roundf(sx * (float)(sc.tex_w - 1u));
+    uint32_t my = (uint32_t)roundf(sy * (float)(sc.tex_h - 1u));
+    const float* p = sc.tex + (size_t)(my * sc.tex_w + mx) * sc.tex_c;
+    out[0] = out[1] = out[2] = out[3] = 0.f;
+    switch (sc.tex_c) {
+    case 1: out[0] = out[1] = out[2] = out[3] = p[0]; break;
+    case 2: out[0] = p[0]; out[1] = p[1]; break;
+    case 3: out[0] = p[0]; out[1] = p[1]; out[2] = p[2]; break;
+    case 4: out[0] = p[0]; out[1] = p[1]; out[2] = p[2]; out[3] = p[3]; break;
+    default: break;
+    }
+}
+
+// cosine-ish hemisphere direction of pathtracer.cpp:155-162 / :175-186 around normal N for incoming rDir
+__device__ __forceinline__ V3 diffuse_dir(V3 N, V3 rDir, float c1, float s1, float r2s, float sq) {
+    V3 w = dot(N, rDir) < 0.f ? N : N * -1.f;
+    V3 u = normalize(cross((double)fabsf(w.x) > .1 ? V3(0, 1, 0) : V3(1, 0, 0), w));
+    V3 v = cross(w, u);
+    return normalize(u * c1 * r2s + v * s1 * r2s + w * sq);
+}
+
+// One iteration of Radiance()'s loop (pathtracer.cpp:36-196) for every queued ray.
+__global__ void __launch_bounds__(kWfBlock) k_shade(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, RoundParams rp,
+                                                    const float4* __restrict__ rays, const float2* __restrict__ hits,
+                                                    const uint32_t* __restrict__ qcount_in, float4* __restrict__ rays_out,
+                                                    uint32_t* __restrict__ qcount_out, float4* __restrict__ radiance, float4* __restrict__ thr,
+                                                    uint2* __restrict__ meta, int radiance_query) {
+    const uint32_t n = *qcount_in;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; base < n; base += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = base + lane;
+        bool alive = false;
+        V3 nStart(0, 0, 0), nDir(0, 0, 0);
+        uint32_t slot = 0;
+        if (i < n) {
+            const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
+            const float2 hr = __ldg(&hits[i]);
+            slot = __float_as_uint(ra.w);
+            V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
+            const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y));
+            float4 acc = radiance[slot];
+            float4 tp = thr[slot];
+            uint2 mt = meta[slot];
+            uint32_t depth = mt.y & 0xFFFFu, segs = mt.y >> 16;
+            ++segs;
+            alive = true;
+            if (!h.hit) alive = false; // :37-41
+            if (alive) {
+                acc.x += tp.x * h.Le.x; acc.y += tp.y * h.Le.y; acc.z += tp.z * h.Le.z; acc.w += tp.w * 0.f; // :43
+                if (depth == 0) acc.w = h.dist; // :44-47
+                if (length(h.Le) > 1.f) alive = false; // :52
+            }
+            if (alive) {
+                // pixel/sample of this slot (Philox counter)
+                uint64_t pixel; uint32_t sample;
+                if (radiance_query) { pixel = slot; sample = 0; }
+                else { map_pixel(pm, rp.lp0 + (slot % rp.n_local), &pixel); sample = rp.s0 + (uint32_t)(slot / rp.n_local); }
+                Rng rng(rp.seed, pixel, sample, mt.x);
+                if (rp.mode == VMN_MODE_FIXED) {
+                    ++depth;
+                    if (segs >= rp.max_segments) alive = false;
+                } else {
+                    ++depth;
+                    if (depth > 5 && (rng.next01() > 0.95f || depth > 1000)) alive = false; // :56-59
+                }
+                if (alive) {
+                    const float r2scale = (rp.mode == VMN_MODE_FIXED) ? 1.f : 10.f;
+                    float sc4[4] = {1.f, 1.f, 1.f, 1.f};
+                    if (h.material && sc.tex) texture_sample(sc, h.uv0, h.uv1, sc4); // :62-80
+                    if (h.material && rng.next01() >= 0.96) { // mirror :98-109
+                        rng.next01(); rng.next01(); rng.next01();
+                        nStart = h.P - rDir * 0.001f;
+                        nDir = normalize(rDir - h.N * 2.f * dot(h.N, rDir));
+                    } else if (h.material) { // diffuse :151-165
+                        tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3];
+                        float r1 = (float)(2 * 3.14159265358979323846 * rng.next01());
+                        float r2 = (float)((double)r2scale * rng.next01());
+                        float r2s = sqrtf(r2);
+                        nDir = diffuse_dir(h.N, rDir, (float)cos((double)r1), (float)sin((double)r1), r2s, sqrtf(1 - r2));
+                        nStart = h.P - rDir * 0.001f;
+                    } else { // sphere-only hit :166-190
+                        double r1 = 2 * 3.14159265358979323846 * rng.next01();
+                        double r2 = (double)r2scale * rng.next01();
+                        float r2s = (float)sqrt(r2);
+                        rng.next01(); rng.next01(); rng.next01();
+                        nDir = diffuse_dir(h.N, rDir, (float)cos(r1), (float)sin(r1), r2s, (float)sqrt(1 - r2));
+                        nStart = h.P - rDir * 0.001f;
+                    }
+                }
+                mt.x = rng.draw;
+            }
+            mt.y = (depth & 0xFFFFu) | (segs << 16);
+            radiance[slot] = acc;
+            thr[slot] = tp;
+            meta[slot] = mt;
+        }
+        const uint32_t ballot = __ballot_sync(0xffffffffu, alive);
+        if (ballot) {
+            const int leader = __ffs(ballot) - 1;
+            uint32_t qb = 0;
+            if ((int)lane == leader) qb = atomicAdd(qcount_out, (uint32_t)__popc(ballot));
+            qb = __shfl_sync(0xffffffffu, qb, leader);
+            if (alive) {
+                const uint32_t q = qb + __popc(ballot & ((1u << lane) - 1u));
+                rays_out[2ull * q] = make_float4(nStart.x, nStart.y, nStart.z, __uint_as_float(slot));
+                rays_out[2ull * q + 1] = make_float4(nDir.x, nDir.y, nDir.z, 0.f);
+            }
+        }
+    }
+}
+
+// ---- accumulate / resolve --------------------------------------------------------------------------
+// FIXED: film[pixel] += the round's `batch` samples, in sample order.
+// COMPAT (batch = 1): additionally the early-out state machine of pathtracer.cpp:242-312.
+__global__ void __launch_bounds__(256) k_accumulate(PixelMap pm, RoundParams rp, uint32_t spp, const float4* __restrict__ radiance,
+                                                    const uint2* __restrict__ meta, float4* __restrict__ film, uint32_t* __restrict__ cstate,
+                                                    uint32_t* __restrict__ live_count) {
+    const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp >= rp.n_local) return;
+    uint64_t pixel;
+    if (!map_pixel(pm, rp.lp0 + lp, &pixel)) return;
+    float4 f = film[pixel];
+    if (rp.mode == VMN_MODE_FIXED) {
+        for (uint32_t k = 0; k < rp.batch; ++k) {
+            const float4 s = radiance[(uint64_t)k * rp.n_local + lp];
+            f.x += s.x; f.y += s.y; f.z += s.z; f.w += 1.f;
+        }
+        film[pixel] = f;
+        return;
+    }
+    uint32_t cs = cstate[lp];
+    if (cs & 0x20000000u) return; // done earlier
+    const float4 s = radiance[lp];
+    f.x += s.x; f.y += s.y; f.z += s.z; f.w += 1.f;
+    film[pixel] = f;
+    uint32_t st = cs >> 30, sz = cs & 0x1FFFFFFFu;
+    const uint32_t n = (uint32_t)f.w;
+    bool brk = false;
+    if ((double)n > sqrt((double)spp)) { // :290
+        const float fn = (float)n, fn1 = (float)(n + 1);
+        V3 a(f.x / fn, f.y / fn, f.z / fn), b((f.x + s.x) / fn1, (f.y + s.y) / fn1, (f.z + s.z) / fn1);
+        if (fabsf(length(a - b)) < 0.00001f) brk = true;
+    }
+    ++sz;
+    bool done = false;
+    if (brk || sz >= rp.per) { sz = 0; if (st == 3) done = true; else ++st; }
+    cstate[lp] = (st << 30) | (done ? 0x20000000u : 0u) | sz;
+    if (!done) atomicAdd(live_count, 1u);
+}
+
+// pathtracer.cpp:318-323 + camera.cpp:106-113
+__global__ void k_resolve(const float4* __restrict__ film, float* __restrict__ out, uint64_t npix) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 f = film[p];
+    float* o = out + 5 * p;
+    if (f.w == 0.f) { o[0] = o[1] = o[2] = o[3] = o[4] = 0.f; return; } // pixel not rendered by anyone
+    o[0] = fmaxf(fminf(f.x / f.w, 1.f), 0.f);
+    o[1] = fmaxf(fminf(f.y / f.w, 1.f), 0.f);
+    o[2] = fmaxf(fminf(f.z / f.w, 1.f), 0.f);
+    o[3] = 1.f;
+    o[4] = f.w;
+}
+
+__global__ void k_camera_rays(CamDev cam, const uint64_t* __restrict__ pixel, const uint32_t* __restrict__ sx, const uint32_t* __restrict__ sy,
+                              const float* __restrict__ jx, const float* __restrict__ jy, uint64_t n, float4* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V3 o, d;
+    camera_ray(cam, pixel[i], sx[i], sy[i], jx[i], jy[i], &o, &d);
+    out[2 * i] = make_float4(o.x, o.y, o.z, 0.f);
+    out[2 * i + 1] = make_float4(d.x, d.y, d.z, 0.f);
+}
+
+// vmn_radiance: turn caller rays into queue entries with slot = index
+__global__ void k_radiance_init(const float4* __restrict__ in, uint64_t n, float4* __restrict__ rays, float4* __restrict__ radiance,
+                                float4* __restrict__ thr, uint2* __restrict__ meta) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 a = in[2 * i], b = in[2 * i + 1];
+    a.w = __uint_as_float((uint32_t)i); b.w = 0.f;
+    rays[2 * i] = a; rays[2 * i + 1] = b;
+    radiance[i] = make_float4(0.f, 0.f, 0.f, -100.f);
+    thr[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+    meta[i] = make_uint2(2u, 0u);
+}
+
+__global__ void k_radiance_out(const float4* __restrict__ radiance, const uint2* __restrict__ meta, uint64_t n, float4* __restrict__ out,
+                               uint32_t* __restrict__ rays_cast) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = radiance[i];
+    rays_cast[i] = meta[i].y >> 16;
+}
+
+// ---- host orchestration ----------------------------------------------------------------------------
+static inline uint32_t cdiv64(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
+
+static CamDev cam_dev(const vmn_ctx* c) {
+    CamDev cd;
+    memcpy(cd.m, c->cam_m, sizeof(cd.m));
+    cd.px = c->cam.position[0]; cd.py = c->cam.position[1]; cd.pz = c->cam.position[2];
+    cd.dist = c->cam.dist_to_film; cd.sx = c->cam.sensor_x; cd.sy = c->cam.sensor_y;
+    cd.width = c->cam.width; cd.height = c->cam.height; cd.spp = c->cam.spp;
+    return cd;
+}
+
+// per-stage device timing: event pairs around launches, summed after the stream drains
+struct StageClock {
+    vmn_ctx* c; PathPool* p;
+    std::vector<std::pair<size_t, int>> spans; // (index of start event, stage)
+    cudaEvent_t get() {
+        if (p->ev_used == p->events.size()) { cudaEvent_t e; cudaEventCreate(&e); p->events.push_back(e); }
+        return p->events[p->ev_used++];
+    }
+    void begin(int stage) { spans.push_back({p->ev_used, stage}); cudaEventRecord(get(), c->stream); }
+    void end() { cudaEventRecord(get(), c->stream); }
+    void collect(double ms[4]) {
+        for (auto& s : spans) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, p->events[s.first], p->events[s.first + 1]) == cudaSuccess) ms[s.second] += t;
+        }
+    }
+};
+enum { ST_RAYGEN = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_RESOLVE = 3 };
+
+static int extend_grid(vmn_ctx* c, bool count) {
+    int per_sm = 0;
+    cudaError_t e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend<true>, kWfBlock, 0)
+                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend<false>, kWfBlock, 0);
+    if (e != cudaSuccess || per_sm < 1) per_sm = 4;
+    return c->sm_count * per_sm;
+}
+
+// ctl layout: [0,32) queue counts (qc[0], qc[1], qc[4] = live pixels); [64, 64+8*kMaxClaims) claim counters — both zeroed every
+// round; [kOffFrame, +32) frame-level counters (nodes, tris, rays), zeroed once per call.
+constexpr uint32_t kMaxClaims = 480;
+constexpr size_t kOffFrame = 4000;
+
+// one extend + shade iteration over queue `cur`; claim counter index `it`
+static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const RoundParams& rp, int cur, uint32_t it, int radiance_query,
+                         StageClock* clk, int grid_extend) {
+    uint32_t* qc = p->ctl.as<uint32_t>();
+    unsigned long long* claims = reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + 64);
+    TravCounters* gcnt = reinterpret_cast<TravCounters*>(p->ctl.as<char>() + kOffFrame);
+    unsigned long long* total = reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + kOffFrame + 16);
+    const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
+    VMN_CUDA(c, cudaMemsetAsync(qc + (cur ^ 1), 0, 4, c->stream));
+    if (clk) clk->begin(ST_EXTEND);
+    if (count)
+        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total);
+    else
+        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total);
+    if (clk) { clk->end(); clk->begin(ST_SHADE); }
+    k_shade<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
+                                                         qc + cur, p->ray[cur ^ 1].as<float4>(), qc + (cur ^ 1), p->radiance.as<float4>(),
+                                                         p->thr.as<float4>(), p->meta.as<uint2>(), radiance_query);
+    if (clk) clk->end();
+    VMN_CUDA(c, cudaGetLastError());
+    c->stats.kernel_launches += 2;
+    return VMN_OK;
+}
+
+
+vmn_status launch_radiance(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint64_t seed, int mode, uint32_t max_segments, float* d_out,
+                           uint32_t* d_rays_cast) {
+    c->stats.kernel_launches = 0; c->stats.rays_traced = 0;
+    if (n == 0) return VMN_OK;
+    if (n >= 0xFFFFFFFFull) return fail(c, VMN_ERR_INVALID, "too many rays");
+    vmn_status s = pool_ensure(c, n);
+    if (s != VMN_OK) return s;
+    PathPool* p = c->pool;
+    uint32_t* qc = p->ctl.as<uint32_t>();
+    VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 4096, c->stream));
+    k_radiance_init<<<cdiv64(n, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_rays), n, p->ray[0].as<float4>(), p->radiance.as<float4>(),
+                                                           p->thr.as<float4>(), p->meta.as<uint2>());
+    const uint32_t n32 = (uint32_t)n;
+    VMN_CUDA(c, cudaMemcpyAsync(qc, &n32, 4, cudaMemcpyHostToDevice, c->stream));
+    PixelMap pm{}; pm.width = 0xFFFFFFFFu; pm.height = 1;
+    RoundParams rp{}; rp.seed = seed; rp.n_local = n; rp.mode = mode; rp.max_segments = max_segments; rp.batch = 1;
+    const int grid = extend_grid(c, (c->flags & VMN_CFG_COUNTERS) != 0);
+    int cur = 0;
+    uint64_t live = n, rays = 0;
+    for (uint32_t it = 0; live; ++it) {
+        if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
+        rays += live;
+        if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 1, nullptr, grid)) != VMN_OK) return s;
+        cur ^= 1;
+        VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + cur, 4, cudaMemcpyDeviceToHost, c->stream));
+        VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+        live = p->h_count[0];
+    }
+    k_radiance_out<<<cdiv64(n, 256), 256, 0, c->stream>>>(p->radiance.as<float4>(), p->meta.as<uint2>(), n, reinterpret_cast<float4*>(d_out), d_rays_cast);
+    VMN_CUDA(c, cudaGetLastError());
+    c->stats.rays_traced = rays; c->stats.paths_traced = n; c->stats.kernel_launches += 2;
+    return VMN_OK;
+}
+
+vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_t* d_sx, const uint32_t* d_sy, const float* d_jx,
+                              const float* d_jy, uint64_t n, vmn_ray* d_out) {
+    if (n == 0) return VMN_OK;
+    k_camera_rays<<<cdiv64(n, 256), 256, 0, c->stream>>>(cam_dev(c), d_pixel, d_sx, d_sy, d_jx, d_jy, n, reinterpret_cast<float4*>(d_out));
+    VMN_CUDA(c, cudaGetLastError());
+    return VMN_OK;
+}
+
+vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix) {
+    if (npix == 0) return VMN_OK;
+    k_resolve<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), d_rgbaz, npix);
+    VMN_CUDA(c, cudaGetLastError());
+    return VMN_OK;
+}
+
+vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
+    const uint64_t npix = c->film_pixels;
+    const uint32_t spp = c->cam.spp;
+    PixelMap pm{};
+    pm.width = c->cam.width; pm.height = c->cam.height;
+    uint64_t n_local_total;
+    if (prm->tile_size) {
+        if (!prm->tile_world || prm->tile_rank >= prm->tile_world) return fail(c, VMN_ERR_INVALID, "bad tile rank/world");
+        pm.tile = prm->tile_size; pm.rank = prm->tile_rank; pm.world = prm->tile_world;
+        pm.tiles_x = (pm.width + pm.tile - 1) / pm.tile;
+        const uint64_t tiles = (uint64_t)pm.tiles_x * ((pm.height + pm.tile - 1) / pm.tile);
+        const uint64_t mine = tiles > pm.rank ? (tiles - pm.rank + pm.world - 1) / pm.world : 0;
+        n_local_total = mine * pm.tile * pm.tile;
+    } else {
+        const uint64_t pe = prm->pixel_end ? prm->pixel_end : npix;
+        if (prm->pixel_begin > pe || pe > npix) return fail(c, VMN_ERR_INVALID, "bad pixel range");
+        pm.begin = prm->pixel_begin;
+        n_local_total = pe - prm->pixel_begin;
+    }
+    const int mode = prm->mode;
+    uint32_t s_begin = 0, s_end = spp;
+    if (mode == VMN_MODE_FIXED) {
+        s_begin = prm->sample_begin; s_end = prm->sample_end ? prm->sample_end : spp;
+        if (s_begin > s_end) return fail(c, VMN_ERR_INVALID, "bad sample range");
+    }
+    c->stats.kernel_launches = 0; c->stats.rays_traced = 0; c->stats.paths_traced = 0;
+    c->stats.raygen_ms = c->stats.extend_ms = c->stats.shade_ms = c->stats.resolve_ms = c->stats.total_ms = 0;
+    VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
+    if (n_local_total == 0 || s_begin == s_end) return VMN_OK;
+
+    const uint64_t cap = c->max_paths;
+    const uint64_t chunk = n_local_total < cap ? n_local_total : cap;
+    uint32_t batch = 1;
+    if (mode == VMN_MODE_FIXED) {
+        batch = (uint32_t)(cap / chunk);
+        if (batch > s_end - s_begin) batch = s_end - s_begin;
+        if (batch < 1) batch = 1;
+    }
+    vmn_status s = pool_ensure(c, chunk * batch);
+    if (s != VMN_OK) return s;
+    PathPool* p = c->pool;
+    if (mode == VMN_MODE_COMPAT && (s = dev_reserve(c, p->cstate, 4 * chunk)) != VMN_OK) return s;
+    p->ev_used = 0;
+    StageClock clk{c, p, {}};
+    uint32_t* qc = p->ctl.as<uint32_t>();
+    const CamDev cd = cam_dev(c);
+    const uint32_t max_seg = prm->max_segments ? prm->max_segments : 5;
+    const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
+    const int grid = extend_grid(c, count);
+    VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + kOffFrame, 0, 32, c->stream));
+
+    VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+    for (uint64_t lp0 = 0; lp0 < n_local_total; lp0 += chunk) {
+        RoundParams rp{};
+        rp.seed = prm->seed; rp.lp0 = lp0; rp.n_local = (n_local_total - lp0 < chunk) ? n_local_total - lp0 : chunk;
+        rp.per = spp / 4; rp.mode = mode; rp.max_segments = max_seg;
+        if (mode == VMN_MODE_COMPAT) {
+            if (rp.per == 0) continue; // spp < 4: the reference takes no samples at all
+            VMN_CUDA(c, cudaMemsetAsync(p->cstate.p, 0, 4 * rp.n_local, c->stream));
+            uint64_t live_px = rp.n_local;
+            for (uint32_t round = 0; live_px; ++round) {
+                rp.s0 = round; rp.batch = 1;
+                VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
+                clk.begin(ST_RAYGEN);
+                k_raygen<<<cdiv64(rp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, p->cstate.as<uint32_t>(), p->ray[0].as<float4>(), qc,
+                                                                                   p->radiance.as<float4>(), p->thr.as<float4>(), p->meta.as<uint2>());
+                clk.end();
+                ++c->stats.kernel_launches;
+                VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
+                VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+                uint64_t live = p->h_count[0];
+                c->stats.paths_traced += live;
+                int cur = 0;
+                for (uint32_t it = 0; live; ++it) {
+                    if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
+                    if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
+                    cur ^= 1;
+                    VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + cur, 4, cudaMemcpyDeviceToHost, c->stream));
+                    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+                    live = p->h_count[0];
+                }
+                VMN_CUDA(c, cudaMemsetAsync(qc + 4, 0, 4, c->stream));
+                clk.begin(ST_RESOLVE);
+                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(), p->meta.as<uint2>(),
+                                                                             c->film.as<float4>(), p->cstate.as<uint32_t>(), qc + 4);
+                clk.end();
+                ++c->stats.kernel_launches;
+                VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + 4, 4, cudaMemcpyDeviceToHost, c->stream));
+                VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+                live_px = p->h_count[0];
+            }
+        } else {
+            for (uint32_t s0 = s_begin; s0 < s_end; s0 += batch) {
+                rp.s0 = s0; rp.batch = (s_end - s0 < batch) ? s_end - s0 : batch;
+                VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
+                clk.begin(ST_RAYGEN);
+                k_raygen<<<cdiv64(rp.n_local * rp.batch, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, nullptr, p->ray[0].as<float4>(), qc,
+                                                                                              p->radiance.as<float4>(), p->thr.as<float4>(),
+                                                                                              p->meta.as<uint2>());
+                clk.end();
+                ++c->stats.kernel_launches;
+                int cur = 0;
+                for (uint32_t it = 0; it < max_seg; ++it) {
+                    if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
+                    cur ^= 1;
+                }
+                clk.begin(ST_RESOLVE);
+                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(), p->meta.as<uint2>(),
+                                                                             c->film.as<float4>(), nullptr, nullptr);
+                clk.end();
+                ++c->stats.kernel_launches;
+                c->stats.paths_traced += rp.n_local * rp.batch;
+            }
+        }
+    }
+    VMN_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    VMN_CUDA(c, cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]);
+    c->stats.total_ms = ms;
+    double st[4] = {0, 0, 0, 0};
+    clk.collect(st);
+    c->stats.raygen_ms = st[ST_RAYGEN]; c->stats.extend_ms = st[ST_EXTEND]; c->stats.shade_ms = st[ST_SHADE]; c->stats.resolve_ms = st[ST_RESOLVE];
+    unsigned long long h[3] = {0, 0, 0};
+    VMN_CUDA(c, cudaMemcpy(h, p->ctl.as<char>() + kOffFrame, 24, cudaMemcpyDeviceToHost));
+    c->stats.nodes_visited = h[0]; c->stats.tris_tested = h[1]; c->stats.rays_traced = h[2];
+    return VMN_OK;
+}
+
+} // namespace vmn

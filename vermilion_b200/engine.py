@@ -1,0 +1,255 @@
+"""ctypes binding of libvermilion_b200.so (include/vermilion_b200.h) — plumbing for tests and bench.py.
+
+The product is the C-ABI library; the reference-side binding is the C++ adapter in vermilion_b200/host/
+(class B200PathTracer : Vermilion::Integrator). This module only marshals numpy arrays across the same ABI.
+There is NO CPU fallback: if the library is missing, or no CUDA device is present, construction raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvermilion_b200.so")
+
+RAY = np.dtype([("o", "<f4", 3), ("pad0", "<f4"), ("d", "<f4", 3), ("pad1", "<f4")])
+HIT = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("tri", "<u4")])
+RAYCAST = np.dtype([("P", "<f4", 3), ("dist", "<f4"), ("N", "<f4", 3), ("flags", "<u4"), ("uv", "<f4", 2),
+                    ("Le", "<f4", 3), ("tri", "<u4"), ("pad", "<u4", 2)])
+SPHERE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("emission", "<f4", 3), ("flags", "<u4"),
+                   ("normal_center", "<f4", 3), ("pad", "<f4")])
+MISS = 0xFFFFFFFF
+MODE_COMPAT, MODE_FIXED = 0, 1
+FILM_RGBAZ, FILM_SUM = 0, 1
+CFG_COUNTERS = 1
+ISECT_BVH2 = 1
+STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE"}
+
+EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vmn_set_stream", "vmn_synchronize",
+           "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
+           "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
+           "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
+           "vmn_film_resolve_device", "vmn_get_stats"]
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("flags", C.c_uint32), ("max_paths", C.c_uint64), ("stream", C.c_void_p)]
+
+
+class Camera(C.Structure):
+    """vmn_camera = the fields of Vermilion::Camera the integrator reads (camera.h:66-104), after its constructor."""
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("position", C.c_float * 3), ("rotation", C.c_float * 3),
+                ("dist_to_film", C.c_float), ("sensor_x", C.c_float), ("sensor_y", C.c_float), ("spp", C.c_uint32)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("max_segments", C.c_uint32), ("seed", C.c_uint64), ("pixel_begin", C.c_uint64),
+                ("pixel_end", C.c_uint64), ("sample_begin", C.c_uint32), ("sample_end", C.c_uint32), ("tile_size", C.c_uint32),
+                ("tile_rank", C.c_uint32), ("tile_world", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_triangles", C.c_uint64), ("n_nodes", C.c_uint64), ("n_wide_nodes", C.c_uint64), ("node_bytes", C.c_uint64),
+                ("tri_bytes", C.c_uint64), ("build_ms", C.c_double), ("rays_traced", C.c_uint64), ("paths_traced", C.c_uint64),
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("extend_ms", C.c_double), ("shade_ms", C.c_double),
+                ("raygen_ms", C.c_double), ("resolve_ms", C.c_double), ("total_ms", C.c_double), ("kernel_launches", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+def camera_from_settings(width, height, position, rotation_deg, back_distance=6.0, back_size=(3.6, 2.4), spp=16):
+    """Vermilion::Camera's constructor (camera.cpp:34-56): degrees -> radians with pi = 3.1415926535 in double, x and y negated."""
+    cam = Camera()
+    cam.width, cam.height = width, height
+    rot = [-float(rotation_deg[0]) * 3.1415926535 / 180, -float(rotation_deg[1]) * 3.1415926535 / 180,
+           float(rotation_deg[2]) * 3.1415926535 / 180]
+    for i in range(3):
+        cam.position[i] = position[i]
+        cam.rotation[i] = np.float32(rot[i])
+    cam.dist_to_film = back_distance
+    cam.sensor_x, cam.sensor_y = back_size
+    cam.spp = spp
+    return cam
+
+
+class VmnError(RuntimeError):
+    pass
+
+
+_LIB = None
+
+
+def load_library():
+    """dlopen the C-ABI library and declare its prototypes. Loads without a GPU (no compute call is made)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise VmnError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, u32, u64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int32
+    L.vmn_abi_version.restype = C.c_int
+    L.vmn_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.vmn_destroy.argtypes = [vp]
+    L.vmn_destroy.restype = None
+    L.vmn_last_error.argtypes = [vp]
+    L.vmn_last_error.restype = C.c_char_p
+    L.vmn_set_stream.argtypes = [vp, vp]
+    L.vmn_synchronize.argtypes = [vp]
+    L.vmn_scene_set_triangles.argtypes = [vp, vp, vp, vp, u64]
+    L.vmn_scene_set_spheres.argtypes = [vp, vp, u32]
+    L.vmn_reference_spheres.argtypes = [vp]
+    L.vmn_reference_spheres.restype = None
+    L.vmn_scene_set_texture.argtypes = [vp, u32, vp, u32, u32, u32]
+    L.vmn_scene_commit.argtypes = [vp]
+    L.vmn_intersect.argtypes = [vp, vp, u64, vp, u32]
+    L.vmn_intersect_device.argtypes = [vp, vp, u64, vp, u32]
+    L.vmn_occluded.argtypes = [vp, vp, u64, vp]
+    L.vmn_raycast.argtypes = [vp, vp, u64, vp]
+    L.vmn_radiance.argtypes = [vp, vp, u64, u64, i32, u32, vp, vp]
+    L.vmn_camera_set.argtypes = [vp, C.POINTER(Camera)]
+    L.vmn_camera_rays.argtypes = [vp, vp, vp, vp, vp, vp, u64, vp]
+    L.vmn_render.argtypes = [vp, C.POINTER(RenderParams)]
+    L.vmn_read_image.argtypes = [vp, vp, i32]
+    L.vmn_film_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
+    L.vmn_film_resolve_device.argtypes = [vp, vp, vp]
+    L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    _LIB = L
+    return L
+
+
+def reference_spheres():
+    s = np.zeros(8, SPHERE)
+    load_library().vmn_reference_spheres(s.ctypes.data_as(C.c_void_p))
+    return s
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Engine:
+    """One vmn_ctx on one CUDA device."""
+
+    def __init__(self, device=0, counters=False, max_paths=0, stream=None):
+        self.L = load_library()
+        self.h = C.c_void_p()
+        cfg = Config(device, CFG_COUNTERS if counters else 0, max_paths, stream)
+        st = self.L.vmn_create(C.byref(cfg), C.byref(self.h))
+        if st != 0:
+            msg = self.L.vmn_last_error(self.h).decode() if self.h else "allocation failed"
+            if self.h:
+                self.L.vmn_destroy(self.h)
+                self.h = C.c_void_p()
+            raise VmnError(f"vmn_create: {STATUS.get(st, st)}: {msg}")
+
+    def _chk(self, st, what):
+        if st != 0:
+            raise VmnError(f"{what}: {STATUS.get(st, st)}: {self.L.vmn_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.vmn_destroy(self.h)
+            self.h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # scene ------------------------------------------------------------------------------------------
+    def set_scene(self, pos, nrm=None, uv=None, spheres=None, texture=None):
+        """spheres: None = the reference's eight (meshEngine.cpp:377-500); an empty array disables them."""
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 9)
+        nrm = None if nrm is None else np.ascontiguousarray(nrm, np.float32).reshape(-1, 9)
+        uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 6)
+        self._chk(self.L.vmn_scene_set_triangles(self.h, _p(pos), _p(nrm), _p(uv), len(pos)), "vmn_scene_set_triangles")
+        sp = reference_spheres() if spheres is None else np.ascontiguousarray(spheres, SPHERE)
+        self._chk(self.L.vmn_scene_set_spheres(self.h, _p(sp) if len(sp) else None, len(sp)), "vmn_scene_set_spheres")
+        if texture is not None:
+            tex = np.ascontiguousarray(texture, np.float32)
+            h, w, c = tex.shape
+            self._chk(self.L.vmn_scene_set_texture(self.h, 0, _p(tex), w, h, c), "vmn_scene_set_texture")
+        self._chk(self.L.vmn_scene_commit(self.h), "vmn_scene_commit")
+
+    # ray queries ------------------------------------------------------------------------------------
+    def intersect(self, rays, flags=0):
+        rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
+        out = np.empty(len(rays), HIT)
+        self._chk(self.L.vmn_intersect(self.h, _p(rays), len(rays), _p(out), flags), "vmn_intersect")
+        return out
+
+    def intersect_device(self, d_rays_ptr, n, d_out_ptr, flags=0):
+        self._chk(self.L.vmn_intersect_device(self.h, d_rays_ptr, n, d_out_ptr, flags), "vmn_intersect_device")
+
+    def occluded(self, rays):
+        rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
+        out = np.empty(len(rays), np.uint8)
+        self._chk(self.L.vmn_occluded(self.h, _p(rays), len(rays), _p(out)), "vmn_occluded")
+        return out
+
+    def raycast(self, rays):
+        rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
+        out = np.empty(len(rays), RAYCAST)
+        self._chk(self.L.vmn_raycast(self.h, _p(rays), len(rays), _p(out)), "vmn_raycast")
+        return out
+
+    def radiance(self, rays, seed, mode=MODE_COMPAT, max_segments=5):
+        rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
+        out = np.empty((len(rays), 4), np.float32)
+        cnt = np.empty(len(rays), np.uint32)
+        self._chk(self.L.vmn_radiance(self.h, _p(rays), len(rays), seed, mode, max_segments, _p(out), _p(cnt)), "vmn_radiance")
+        return out, cnt
+
+    # camera / render --------------------------------------------------------------------------------
+    def set_camera(self, cam):
+        self.cam = cam
+        self._chk(self.L.vmn_camera_set(self.h, C.byref(cam)), "vmn_camera_set")
+
+    def camera_rays(self, pixel, sx, sy, jx, jy):
+        pixel = np.ascontiguousarray(pixel, np.uint64)
+        sx = np.ascontiguousarray(sx, np.uint32)
+        sy = np.ascontiguousarray(sy, np.uint32)
+        jx = np.ascontiguousarray(jx, np.float32)
+        jy = np.ascontiguousarray(jy, np.float32)
+        out = np.empty(len(pixel), RAY)
+        self._chk(self.L.vmn_camera_rays(self.h, _p(pixel), _p(sx), _p(sy), _p(jx), _p(jy), len(pixel), _p(out)), "vmn_camera_rays")
+        return out
+
+    def render(self, mode=MODE_FIXED, seed=1, max_segments=5, pixel_begin=0, pixel_end=0, sample_begin=0, sample_end=0, tile_size=0,
+               tile_rank=0, tile_world=1):
+        prm = RenderParams(mode, max_segments, seed, pixel_begin, pixel_end, sample_begin, sample_end, tile_size, tile_rank, tile_world, 0)
+        self._chk(self.L.vmn_render(self.h, C.byref(prm)), "vmn_render")
+
+    def read_image(self, layout=FILM_RGBAZ):
+        npx = self.cam.width * self.cam.height
+        out = np.empty((npx, 5 if layout == FILM_RGBAZ else 4), np.float32)
+        self._chk(self.L.vmn_read_image(self.h, _p(out), layout), "vmn_read_image")
+        return out
+
+    def film_device(self):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        self._chk(self.L.vmn_film_device(self.h, C.byref(ptr), C.byref(n)), "vmn_film_device")
+        return ptr.value, n.value
+
+    def resolve_device(self, d_sum_ptr):
+        npx = self.cam.width * self.cam.height
+        out = np.empty((npx, 5), np.float32)
+        self._chk(self.L.vmn_film_resolve_device(self.h, d_sum_ptr, _p(out)), "vmn_film_resolve_device")
+        return out
+
+    def set_stream(self, stream_ptr):
+        self._chk(self.L.vmn_set_stream(self.h, stream_ptr), "vmn_set_stream")
+
+    def synchronize(self):
+        self._chk(self.L.vmn_synchronize(self.h), "vmn_synchronize")
+
+    def stats(self):
+        s = Stats()
+        self._chk(self.L.vmn_get_stats(self.h, C.byref(s)), "vmn_get_stats")
+        return s.as_dict()
