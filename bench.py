@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the B200 path-tracing hot path on BASELINE.json's configs[1] (C2):
+procedural tessellated-sphere scene, 983 040 triangles, 1920x1080, 64 spp, primary + 4 bounces (FIXED mode).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--spp S] [--res WxH]
+
+A step = one full frame through the wavefront (raygen -> 5 x (extend, shade) -> accumulate per sample batch).
+N > 1 (torchrun, one rank per GPU): sample-slice split — every rank renders the full frame for its own 64-sample
+slice of an N*64-spp frame (weak scaling), then the film sums are all-reduced with NCCL inside the timed region.
+`value`   device-timed, scene resident in HBM.            `e2e`  through the C ABI with host buffers: scene upload
++ GPU BVH build + render + image read-back every step.    `roofline`  for the dominant kernel (k_extend).
+`cpu_baseline` / --impl reference: the reference's own CPU code (oracle/_ref, -Ofast as shipped) on the host cores.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "C2: 12 icospheres x 81920 = 983040 triangles in the reference room, 1920x1080, 64 spp, FIXED mode, <=5 segments/path"
+CAM_POS, CAM_ROT = (0.0, 500.0, 1900.0), (0.0, 0.0, 0.0)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_scene():
+    from vermilion_b200 import scenes
+    return scenes.spheres(4, 3, 6, 150.0)
+
+
+def make_camera(width, height, spp):
+    from vermilion_b200 import engine
+    return engine.camera_from_settings(width, height, CAM_POS, CAM_ROT, 6.0, (3.6, 3.6 * height / width), spp)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---- CPU reference arm ----------------------------------------------------------------------------------------
+def cpu_reference_sample(pos, nrm, uv, width, height, spp, budget_s=20.0, threads=0):
+    """Times the reference's own CPU code (oracle/_ref/libvermref_ofast.so: unmodified Triangle/BVH/MeshEngine::RayCast, -Ofast as
+    shipped) on a bounded sample of the workload: horizontal 1-row bands spread over the frame, all `spp` samples, FIXED mode.
+    Rays are counted by the bit-identical oracle port on the same pixels (untimed). Falls back to the port if _ref is absent."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import checker
+    cs = checker.camera_settings(width, height, CAM_POS, CAM_ROT, 6.0, (3.6, 3.6 * height / width), spp)
+    kind = "reference" if checker.Ref.available("ofast") else "port"
+    orc = checker.Oracle(pos, nrm, uv)
+    ocam = checker.camera_fields_py(cs)
+    t_build0 = time.time()
+    ref = checker.Ref(pos, nrm, uv, variant="ofast") if kind == "reference" else None
+    build_s = time.time() - t_build0
+    cores = checker.Oracle.max_threads() if threads <= 0 else threads
+    rows = [int((k + 0.5) * height / 16) for k in range(16)]
+    secs, rays, paths, used = 0.0, 0, 0, 0
+    for r in rows:
+        p0, p1 = r * width, (r + 1) * width
+        t0 = time.time()
+        if ref is not None:
+            ref.render_seeded(cs, mode=checker.MODE_FIXED, seed=1, p0=p0, p1=p1, s0=0, s1=spp, max_segments=5, threads=threads)
+        else:
+            orc.render(ocam, checker.MODE_FIXED, checker.RNG_MT64, 1, p0, p1, 0, spp, 5, threads)
+        secs += time.time() - t0
+        _, n = orc.render(ocam, checker.MODE_FIXED, checker.RNG_MT64, 1, p0, p1, 0, spp, 5, 0)
+        rays += n
+        paths += width * spp
+        used += 1
+        if secs > budget_s:
+            break
+    return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
+            "sample": f"{used} one-pixel-high rows spread over the {width}x{height} frame, all {spp} spp, FIXED mode: {paths} paths, {rays} rays in "
+                      f"{secs:.1f} s (reference BVH build {build_s:.1f} s not included)",
+            "spp_per_s": paths / secs / (width * height)}
+
+
+def run_reference(args, width, height):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pos, nrm, uv = make_scene()
+    vals = []
+    t_all = time.time()
+    for i in range(args.warmup + args.steps):
+        r = cpu_reference_sample(pos, nrm, uv, width, height, args.spp, budget_s=args.cpu_budget / max(1, args.warmup + args.steps))
+        if i >= args.warmup:
+            vals.append(r)
+    v = float(np.mean([x["value"] for x in vals]))
+    last = vals[-1]
+    last["value"] = v
+    print(json.dumps({"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+                      "warmup": args.warmup, "ms_per_step": (time.time() - t_all) * 1000 / (args.warmup + args.steps), "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": WORKLOAD, "resolution": f"{width}x{height}", "spp": args.spp}, "cpu_baseline": last,
+                      "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ---- GPU arm --------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--res", default="1920x1080")
+    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--max-paths", type=int, default=8 << 20)
+    args = ap.parse_args()
+    width, height = (int(x) for x in args.res.lower().split("x"))
+    if args.impl == "reference":
+        return run_reference(args, width, height)
+
+    import torch
+    import torch.distributed as dist
+    from vermilion_b200 import engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+
+    pos, nrm, uv = make_scene()
+    spp_total = args.spp * world
+    cam = make_camera(width, height, spp_total)
+    npix = width * height
+
+    def new_engine(counters=False):
+        e = engine.Engine(device=local, counters=counters, max_paths=args.max_paths, stream=stream.cuda_stream)
+        return e
+
+    eng = new_engine()
+    eng.set_scene(pos, nrm, uv)
+    eng.set_camera(cam)
+    d_film, n_floats = eng.film_device()
+    film_t = None
+    if world > 1:
+        # torch view of the context's film buffer for the NCCL all-reduce
+        class _Ptr:
+            pass
+        holder = _Ptr()
+        holder.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (d_film, False), "version": 3}
+        film_t = torch.as_tensor(holder, device=torch.device("cuda", local))
+
+    s0, s1 = rank * args.spp, (rank + 1) * args.spp
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def step():
+        eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
+        if world > 1:
+            dist.all_reduce(film_t)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    rays = extend_ms = launches = 0
+    for a, b in ev:
+        flush.zero_()
+        a.record(stream)
+        step()
+        b.record(stream)
+        b.synchronize()
+        st = eng.stats()
+        rays += st["rays_traced"]; extend_ms += st["extend_ms"]; launches += st["kernel_launches"]
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms, float(rays), extend_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms, rays_all = float(tmax[0]), float(tsum[1])
+    else:
+        rays_all = float(rays)
+    value = rays_all / (ms / 1e3) / 1e6
+    paths_all = float(npix) * args.spp * world * args.steps
+
+    # ---- e2e: host buffers through the C ABI, every step: scene upload + BVH build + render + image read-back ----
+    ppos = torch.from_numpy(pos).pin_memory().numpy(); pnrm = torch.from_numpy(nrm).pin_memory().numpy(); puv = torch.from_numpy(uv).pin_memory().numpy()
+    e2e_steps = max(1, min(args.steps, 3))
+    barrier()
+    t0 = time.perf_counter()
+    e2e_rays = 0
+    for _ in range(e2e_steps):
+        eng.set_scene(ppos, pnrm, puv)
+        eng.set_camera(cam)
+        eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
+        if world > 1:
+            dist.all_reduce(film_t)
+            img = eng.resolve_device(d_film)
+        else:
+            img = eng.read_image()
+        e2e_rays += eng.stats()["rays_traced"]
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        a = te.clone(); dist.all_reduce(a, op=dist.ReduceOp.MAX)
+        b = te.clone(); dist.all_reduce(b, op=dist.ReduceOp.SUM)
+        e2e_s, e2e_rays = float(a[0]), float(b[1])
+    e2e = {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(pos.nbytes + nrm.nbytes + uv.nbytes + 8 * 64 + 48),
+           "d2h_bytes_per_step": int(img.nbytes), "steps": e2e_steps,
+           "includes": "vmn_scene_set_triangles (H2D from pinned host) + vmn_scene_commit (GPU BVH build) + vmn_render + vmn_read_image (D2H)"}
+    build_ms = eng.stats()["build_ms"]
+
+    if rank != 0:
+        eng.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel: measured visits per ray from a counting build on the same frame (untimed) ----
+    ce = new_engine(counters=True)
+    ce.set_scene(pos, nrm, uv)
+    ce.set_camera(make_camera(width, height, 4))
+    ce.render(mode=engine.MODE_FIXED, seed=1, max_segments=5)
+    cst = ce.stats()
+    ce.close()
+    nodes_per_ray = cst["nodes_visited"] / max(1, cst["rays_traced"])
+    tris_per_ray = cst["tris_tested"] / max(1, cst["rays_traced"])
+    b_ray = 32 + 8 + nodes_per_ray * cst["node_bytes"] + tris_per_ray * cst["tri_bytes"]
+    peak, peak_src = peaks()
+    achieved = (rays / max(1e-9, extend_ms / 1e3)) * b_ray / 1e9
+    n_extend = args.steps * 5 * -(-(npix * args.spp) // (args.max_paths // npix * npix if args.max_paths >= npix else args.max_paths))
+    roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "bytes_per_ray": b_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
+                "node_bytes": cst["node_bytes"], "tri_bytes": cst["tri_bytes"], "extend_ms_per_step": extend_ms / args.steps,
+                "extend_share_of_step": extend_ms / ms if world == 1 else None, "extend_launches": int(n_extend),
+                "note": "algorithmic bytes; the 52 MB scene is L2-resident on this config, so achieved can exceed the HBM copy peak"}
+
+    cpu = None
+    if not args.no_cpu and world == 1:
+        try:
+            cpu = cpu_reference_sample(pos, nrm, uv, width, height, args.spp, budget_s=args.cpu_budget)
+        except Exception as e:  # the checker is optional for the GPU number
+            cpu = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "unavailable", "sample": repr(e)}
+
+    out = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": WORKLOAD, "resolution": f"{width}x{height}", "spp_per_gpu": args.spp, "spp_total": spp_total,
+                      "parallelism": f"sample-slice x{world} + NCCL all-reduce of the film" if world > 1 else "single GPU",
+                      "l2": "256 MiB L2 flush between timed steps", "paths_in_flight": args.max_paths},
+           "spp_per_s": paths_all / npix / (ms / 1e3), "rays_per_step": rays_all / args.steps, "bvh_build_ms": build_ms,
+           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

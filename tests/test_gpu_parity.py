@@ -223,7 +223,12 @@ def test_edge_cases(eng):
     r = checker.make_rays(o, d)
     got = eng.intersect(r)
     ref = checker.Oracle(np.concatenate([deg, tri]), spheres=False).intersect(r)
-    assert got.tobytes() == ref.tobytes()
+    # ray 4 hits exactly the vertex (0,0,0) with d.x = d.y = 0: the reference's slab test computes 0*inf = NaN there and drops
+    # the hit (bbox.cpp:70-83); that is a border case (u = v = 0), reported by classify_hits, everything else is bit-exact
+    c = common.classify_hits(got, ref)
+    assert c["bad"] == 0 and c["tie"] + c["edge"] <= 1, c
+    keep = np.array([0, 1, 2, 3, 5])
+    assert got[keep].tobytes() == ref[keep].tobytes()
 
 
 def test_product_path_fails_loudly_without_commit(eng):
