@@ -3,6 +3,7 @@
 #include "common.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -75,6 +76,7 @@ void dev_free(DevBuf& b);
 vmn_status build_bvh(vmn_ctx* c);
 
 // traverse.cu
+uint32_t refill_min(); // idle lanes that trigger a refill in the persistent kernels (env VMN_REFILL, default 8)
 vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags);
 vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_t* d_out);
 vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_raycast_rec* d_out);

@@ -39,23 +39,35 @@ __device__ __forceinline__ uint32_t closest_hit(const SceneDev& sc, V3 o, V3 d, 
 
 template <bool WIDE, bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
-                                                           vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt) {
+                                                           vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt,
+                                                           uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
-    uint64_t i;
-    while (claim_rays(next, n, &i)) {
-        if (i >= n) continue;
-        V3 o, d;
-        load_ray(rays, i, &o, &d);
-        float t;
-        const uint32_t id = closest_hit<WIDE, COUNT>(sc, o, d, &t, sstack, &cnt);
+    auto finish = [&](uint64_t i, V3 o, V3 d, float t, uint32_t k, const TriRec* base) {
+        uint32_t id = VMN_MISS;
         float u = 0.f, v = 0.f;
-        if (id != VMN_MISS) {
+        if (k != VMN_MISS) {
+            id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(base + k)->w));
             const V3 hp = o + d * t; // bvh.cpp:140
             tri_bary(load_tri(sc.tris_orig + id), hp, &u, &v);
         }
         reinterpret_cast<float4*>(out)[i] = make_float4(t, u, v, __uint_as_float(id));
+    };
+    if (WIDE) {
+        persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, &cnt,
+                                [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
+                                [&](uint64_t i, const Trav& s) { finish(i, s.o, s.d, s.best_t, s.best, sc.tris); });
+    } else {
+        uint64_t i;
+        while (claim_rays(next, n, &i)) {
+            if (i >= n) continue;
+            V3 o, d;
+            load_ray(rays, i, &o, &d);
+            float t;
+            const uint32_t k = trace_bvh2<COUNT>(sc, o, d, &t, &cnt);
+            finish(i, o, d, t, k, sc.tris_sorted);
+        }
     }
     if (COUNT) {
         atomicAdd(&gcnt->nodes, cnt.nodes);
@@ -105,6 +117,11 @@ static int resident_grid(vmn_ctx* c, K kernel) {
     return c->sm_count * per_sm;
 }
 
+uint32_t refill_min() {
+    static const uint32_t v = [] { const char* e = getenv("VMN_REFILL"); int x = e ? atoi(e) : 8; return (uint32_t)(x < 1 ? 1 : (x > 32 ? 32 : x)); }();
+    return v;
+}
+
 static vmn_status reset_counters(vmn_ctx* c) {
     vmn_status s = dev_reserve(c, c->counters, 64);
     if (s != VMN_OK) return s;
@@ -123,7 +140,7 @@ vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_h
     if (n) {
         VMN_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
 #define LAUNCH(W, C)                                                                                                           \
-    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt)
+    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt, refill_min())
         if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
         else { if (count) LAUNCH(false, true); else LAUNCH(false, false); }
 #undef LAUNCH

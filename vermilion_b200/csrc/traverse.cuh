@@ -26,7 +26,8 @@ __device__ __forceinline__ bool tri_intersect(const TriRec& T, V3 o, V3 d, float
     V3 v0(T.r0.x, T.r0.y, T.r0.z), e1(T.r1.x, T.r1.y, T.r1.z), e2(T.r2.x, T.r2.y, T.r2.z);
     V3 pvec = cross(d, e2);
     float det = dot(e1, pvec);
-    if ((double)det < 1e-8 && (double)det > -1e-8) return false; // :25, compared as double
+    // :25 compares (double)det with +-1e-8; (float)1e-8 = 0x1.5798eep-27 < 1e-8, so for a float det that is |det| <= (float)1e-8
+    if (fabsf(det) <= 0x1.5798eep-27f) return false;
     float inv_det = 1 / det;
     V3 tvec = o - v0;
     float u = dot(tvec, pvec) * inv_det;
@@ -55,93 +56,181 @@ __device__ __forceinline__ float safe_inv(float x) {
 }
 
 // ---- compressed BVH8 closest hit --------------------------------------------------------------
-// sstack: this thread's slice of the shared-memory stack, entries `sstride` uint2 apart.
-// Returns the index into sc.tris of the closest triangle (or VMN_MISS) and its t.
+// Traversal state of one ray, kept in registers so that a lane can finish one ray and start the next inside the
+// same persistent warp (see k_extend). sstack: this thread's slice of the shared-memory stack, entries `sstride`
+// uint2 apart; deeper entries spill to a small local-memory array.
+struct Trav {
+    V3 o, d;
+    float idx, idy, idz;
+    uint32_t oct_inv;
+    uint2 ng, tg;   // node group: (first child index, hit bits 31..24 | imask 7..0); triangle group: (base, hit bits 23..0)
+    int sp;
+    float best_t;
+    uint32_t best;  // index into sc.tris
+};
+
+// quantised byte j of word w as an exact float: PRMT builds 0x4B0000qq = 2^23 + q, one FADD removes the bias.
+// (I2F.U8 runs on the quarter-rate XU pipe and was 33 % of all stall samples in the first profile.)
+template <int J>
+__device__ __forceinline__ float byte_to_float(uint32_t w) {
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | J)) - 8388608.0f;
+}
+
+__device__ __forceinline__ bool trav_init(Trav& s, const SceneDev& sc, V3 o, V3 d) {
+    s.o = o; s.d = d;
+    s.best_t = VMN_T_MISS; s.best = VMN_MISS;
+    s.sp = 0;
+    s.ng = make_uint2(0u, 0x80000000u); // root: one pending hit at bit 31, imask 0
+    s.tg = make_uint2(0u, 0u);
+    if (sc.n_tris == 0 || ray_is_nan(o, d)) return false; // nothing to traverse: miss
+    s.idx = safe_inv(d.x); s.idy = safe_inv(d.y); s.idz = safe_inv(d.z);
+    s.oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
+    return true;
+}
+
+template <int J>
+__device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint32_t nyw, uint32_t nzw, uint32_t fxw, uint32_t fyw, uint32_t fzw,
+                                              float ax, float ay, float az, float bx, float by, float bz, float best_t, uint32_t oct_inv) {
+    const float tnx = __fmaf_rn(byte_to_float<J>(nxw), ax, bx);
+    const float tny = __fmaf_rn(byte_to_float<J>(nyw), ay, by);
+    const float tnz = __fmaf_rn(byte_to_float<J>(nzw), az, bz);
+    const float tfx = __fmaf_rn(byte_to_float<J>(fxw), ax, bx);
+    const float tfy = __fmaf_rn(byte_to_float<J>(fyw), ay, by);
+    const float tfz = __fmaf_rn(byte_to_float<J>(fzw), az, bz);
+    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
+    if (tn <= tf) {
+        const uint32_t m = (metaw >> (8 * J)) & 0xFFu;
+        const uint32_t inner = ((m & 0x18u) == 0x18u) ? 7u : 0u;
+        const uint32_t bitidx = (m ^ (oct_inv & inner)) & 0x1Fu;
+        return (m >> 5) << bitidx;
+    }
+    return 0u;
+}
+
+// One traversal step: visit the next pending node (8 child boxes), test the triangles it exposes, pop if nothing is
+// pending. Returns false when the ray is finished.
+template <bool COUNT>
+__device__ __forceinline__ bool trav_step(Trav& s, const SceneDev& sc, uint2* sstack, uint32_t sstride, uint2* lstack, TravCounters* cnt) {
+    const uint4* __restrict__ nodes = reinterpret_cast<const uint4*>(sc.nodes);
+    if (s.ng.y & 0xFF000000u) {
+        const uint32_t bit = 31u - __clz(s.ng.y);
+        const uint32_t slot = (bit - 24u) ^ s.oct_inv;
+        s.ng.y &= ~(1u << bit);
+        const uint32_t rel = __popc(s.ng.y & 0xFFu & ((1u << slot) - 1u));
+        const uint32_t nidx = s.ng.x + rel;
+        if (s.ng.y & 0xFF000000u) { // siblings still pending
+            if (s.sp < VMN_SH_STACK) sstack[s.sp * sstride] = s.ng; else lstack[s.sp - VMN_SH_STACK] = s.ng;
+            ++s.sp;
+        }
+        const uint4* np = nodes + 5ull * nidx;
+        const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
+        if (COUNT) ++cnt->nodes;
+        const float ax = __uint_as_float((q0.w & 0xFFu) << 23) * s.idx;
+        const float ay = __uint_as_float(((q0.w >> 8) & 0xFFu) << 23) * s.idy;
+        const float az = __uint_as_float(((q0.w >> 16) & 0xFFu) << 23) * s.idz;
+        const float bx = (__uint_as_float(q0.x) - s.o.x) * s.idx;
+        const float by = (__uint_as_float(q0.y) - s.o.y) * s.idy;
+        const float bz = (__uint_as_float(q0.z) - s.o.z) * s.idz;
+        // near/far byte planes per axis (two words = 8 children each)
+        const bool ngx = s.d.x < 0.f, ngy = s.d.y < 0.f, ngz = s.d.z < 0.f;
+        const uint32_t nx0 = ngx ? q3.z : q2.x, nx1 = ngx ? q3.w : q2.y, fx0 = ngx ? q2.x : q3.z, fx1 = ngx ? q2.y : q3.w;
+        const uint32_t ny0 = ngy ? q4.x : q2.z, ny1 = ngy ? q4.y : q2.w, fy0 = ngy ? q2.z : q4.x, fy1 = ngy ? q2.w : q4.y;
+        const uint32_t nz0 = ngz ? q4.z : q3.x, nz1 = ngz ? q4.w : q3.y, fz0 = ngz ? q3.x : q4.z, fz1 = ngz ? q3.y : q4.w;
+        uint32_t hitmask = 0;
+#define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, ax, ay, az, bx, by, bz, s.best_t, s.oct_inv)
+        VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
+        VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
+#undef VMN_CH
+        s.ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
+        s.tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
+    } else {
+        s.tg = s.ng;
+        s.ng = make_uint2(0u, 0u);
+    }
+    while (s.tg.y) {
+        const uint32_t i = __ffs(s.tg.y) - 1u;
+        s.tg.y &= s.tg.y - 1u;
+        const uint32_t ti = s.tg.x + i;
+        const TriRec T = load_tri(sc.tris + ti);
+        if (COUNT) ++cnt->tris;
+        float ct;
+        if (tri_intersect(T, s.o, s.d, &ct) && ct < s.best_t) { s.best_t = ct; s.best = ti; }
+    }
+    if ((s.ng.y & 0xFF000000u) == 0u) {
+        if (s.sp == 0) return false;
+        --s.sp;
+        s.ng = (s.sp < VMN_SH_STACK) ? sstack[s.sp * sstride] : lstack[s.sp - VMN_SH_STACK];
+    }
+    return true;
+}
+
+// single-ray form: returns the index into sc.tris of the closest triangle (or VMN_MISS) and its t
 template <bool COUNT>
 __device__ __forceinline__ uint32_t trace_wide(const SceneDev& sc, V3 o, V3 d, float* t_out, uint2* sstack, uint32_t sstride,
                                                TravCounters* cnt) {
-    float best_t = VMN_T_MISS;
-    uint32_t best = VMN_MISS;
-    if (sc.n_tris == 0 || ray_is_nan(o, d)) { *t_out = best_t; return best; }
-    const float idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
-    const uint32_t oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
+    Trav s;
     uint2 lstack[VMN_LOCAL_STACK];
-    int sp = 0;
-    uint2 ng = make_uint2(0u, 0x80000000u); // root: one pending hit at bit 31, imask 0
-    uint2 tg = make_uint2(0u, 0u);
-    const uint4* __restrict__ nodes = reinterpret_cast<const uint4*>(sc.nodes);
+    if (trav_init(s, sc, o, d))
+        while (trav_step<COUNT>(s, sc, sstack, sstride, lstack, cnt)) {}
+    *t_out = s.best_t;
+    return s.best;
+}
 
+// ---- persistent lanes ----------------------------------------------------------------------------------------------
+// Every lane of a persistent warp owns one ray at a time. A warp claims CHUNKS of consecutive rays from the global
+// counter (one atomicAdd per chunk, by one lane, broadcast with a shuffle) and hands them to idle lanes by ballot/popc
+// rank, as soon as at least `refill_min` lanes are idle. The first profile of the one-batch-per-warp version showed
+// 3.4 of 32 threads active per instruction: a few long rays kept a warp alive while the other lanes sat finished.
+// load(i, &o, &d) reads ray i; store(i, trav) writes its result.
+template <bool COUNT, class LoadRay, class StoreHit>
+__device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n, unsigned long long* next, uint32_t chunk, uint32_t refill_min,
+                                                 uint2* sstack, uint32_t sstride, TravCounters* cnt, LoadRay load, StoreHit store) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t FULL = 0xffffffffu;
+    Trav s;
+    uint2 lstack[VMN_LOCAL_STACK];
+    bool active = false, exhausted = false;
+    uint64_t ray = 0, wbase = 0;
+    uint32_t wleft = 0; // warp-uniform: rays left in the claimed chunk [wbase, wbase + wleft)
     while (true) {
-        if (ng.y & 0xFF000000u) {
-            const uint32_t bit = 31u - __clz(ng.y);
-            const uint32_t slot = (bit - 24u) ^ oct_inv;
-            ng.y &= ~(1u << bit);
-            const uint32_t rel = __popc(ng.y & 0xFFu & ((1u << slot) - 1u));
-            const uint32_t nidx = ng.x + rel;
-            if (ng.y & 0xFF000000u) { // siblings still pending
-                if (sp < VMN_SH_STACK) sstack[sp * sstride] = ng; else lstack[sp - VMN_SH_STACK] = ng;
-                ++sp;
+        const uint32_t idle = __ballot_sync(FULL, !active);
+        if (idle != 0u && !exhausted && (idle == FULL || (uint32_t)__popc(idle) >= refill_min)) {
+            if (wleft == 0u) {
+                unsigned long long b = 0;
+                if (lane == 0) b = atomicAdd(next, (unsigned long long)chunk);
+                b = __shfl_sync(FULL, b, 0);
+                if (b >= n) exhausted = true;
+                else { wbase = b; wleft = (uint32_t)((n - b < chunk) ? (n - b) : chunk); }
             }
-            const uint4* np = nodes + 5ull * nidx;
-            const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
-            if (COUNT) ++cnt->nodes;
-            const float ax = __uint_as_float((q0.w & 0xFFu) << 23) * idx;
-            const float ay = __uint_as_float(((q0.w >> 8) & 0xFFu) << 23) * idy;
-            const float az = __uint_as_float(((q0.w >> 16) & 0xFFu) << 23) * idz;
-            const float bx = (__uint_as_float(q0.x) - o.x) * idx;
-            const float by = (__uint_as_float(q0.y) - o.y) * idy;
-            const float bz = (__uint_as_float(q0.z) - o.z) * idz;
-            // near/far byte planes per axis (two words = 8 children each)
-            uint32_t nx[2], fx[2], ny[2], fy[2], nz[2], fz[2];
-            if (d.x < 0.f) { nx[0] = q3.z; nx[1] = q3.w; fx[0] = q2.x; fx[1] = q2.y; } else { nx[0] = q2.x; nx[1] = q2.y; fx[0] = q3.z; fx[1] = q3.w; }
-            if (d.y < 0.f) { ny[0] = q4.x; ny[1] = q4.y; fy[0] = q2.z; fy[1] = q2.w; } else { ny[0] = q2.z; ny[1] = q2.w; fy[0] = q4.x; fy[1] = q4.y; }
-            if (d.z < 0.f) { nz[0] = q4.z; nz[1] = q4.w; fz[0] = q3.x; fz[1] = q3.y; } else { nz[0] = q3.x; nz[1] = q3.y; fz[0] = q4.z; fz[1] = q4.w; }
-            const uint32_t meta[2] = {q1.z, q1.w};
-            uint32_t hitmask = 0;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t sh = 8u * j;
-                    const uint32_t m = (meta[h] >> sh) & 0xFFu;
-                    const float tnx = __fmaf_rn((float)((nx[h] >> sh) & 0xFFu), ax, bx);
-                    const float tny = __fmaf_rn((float)((ny[h] >> sh) & 0xFFu), ay, by);
-                    const float tnz = __fmaf_rn((float)((nz[h] >> sh) & 0xFFu), az, bz);
-                    const float tfx = __fmaf_rn((float)((fx[h] >> sh) & 0xFFu), ax, bx);
-                    const float tfy = __fmaf_rn((float)((fy[h] >> sh) & 0xFFu), ay, by);
-                    const float tfz = __fmaf_rn((float)((fz[h] >> sh) & 0xFFu), az, bz);
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
-                    if (tn <= tf) {
-                        const uint32_t inner = ((m & 0x18u) == 0x18u) ? 7u : 0u;
-                        const uint32_t bitidx = (m ^ (oct_inv & inner)) & 0x1Fu;
-                        hitmask |= (m >> 5) << bitidx;
-                    }
+            const uint32_t need = (uint32_t)__popc(idle);
+            const uint32_t take = need < wleft ? need : wleft;
+            if (!active) {
+                const uint32_t r = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (r < take) {
+                    V3 o, d;
+                    ray = wbase + r;
+                    load(ray, &o, &d);
+                    if (trav_init(s, sc, o, d)) active = true; else store(ray, s);
                 }
             }
-            ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
-            tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
-        } else {
-            tg = ng;
-            ng = make_uint2(0u, 0u);
+            wbase += take; wleft -= take;
         }
-        while (tg.y) {
-            const uint32_t i = __ffs(tg.y) - 1u;
-            tg.y &= tg.y - 1u;
-            const uint32_t ti = tg.x + i;
-            const TriRec T = load_tri(sc.tris + ti);
-            if (COUNT) ++cnt->tris;
-            float ct;
-            if (tri_intersect(T, o, d, &ct) && ct < best_t) { best_t = ct; best = ti; }
+        if (__ballot_sync(FULL, active) == 0u) {
+            if (exhausted) break;
+            continue;
         }
-        if ((ng.y & 0xFF000000u) == 0u) {
-            if (sp == 0) break;
-            --sp;
-            ng = (sp < VMN_SH_STACK) ? sstack[sp * sstride] : lstack[sp - VMN_SH_STACK];
+        if (active && !trav_step<COUNT>(s, sc, sstack, sstride, lstack, cnt)) {
+            store(ray, s);
+            active = false;
         }
     }
-    *t_out = best_t;
-    return best;
+}
+
+__device__ __forceinline__ uint32_t pick_chunk(uint64_t n, uint32_t warps) {
+    uint64_t c = n / ((uint64_t)warps * 4u);
+    c = c < 32 ? 32 : (c > 256 ? 256 : c);
+    return (uint32_t)(c & ~31ull);
 }
 
 // ---- binary LBVH closest hit (baseline / cross-check; stack in local memory) --------------------

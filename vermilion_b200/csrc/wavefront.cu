@@ -163,26 +163,22 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
 template <bool COUNT>
 __global__ void __launch_bounds__(kWfBlock) k_extend(SceneDev sc, const float4* __restrict__ rays, const uint32_t* __restrict__ qcount,
                                                      float2* __restrict__ hits, unsigned long long* next, TravCounters* gcnt,
-                                                     unsigned long long* total_rays) {
+                                                     unsigned long long* total_rays, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
     uint2* sstack = sstack_all + threadIdx.x;
     const uint64_t n = *qcount;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total_rays, (unsigned long long)n);
     TravCounters cnt{0ull, 0ull};
-    while (true) {
-        unsigned long long base = 0;
-        if ((threadIdx.x & 31) == 0) base = atomicAdd(next, 32ull);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const uint64_t i = base + (threadIdx.x & 31);
-        if (i >= n) continue;
-        const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
-        float t;
-        const uint32_t k = trace_wide<COUNT>(sc, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), &t, sstack, kWfBlock, &cnt);
-        uint32_t id = VMN_MISS;
-        if (k != VMN_MISS) id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + k)->w));
-        hits[i] = make_float2(t, __uint_as_float(id));
-    }
+    persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, &cnt,
+                            [&](uint64_t i, V3* o, V3* d) {
+                                const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
+                                *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
+                            },
+                            [&](uint64_t i, const Trav& s) {
+                                uint32_t id = VMN_MISS;
+                                if (s.best != VMN_MISS) id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + s.best)->w));
+                                hits[i] = make_float2(s.best_t, __uint_as_float(id));
+                            });
     if (COUNT) { atomicAdd(&gcnt->nodes, cnt.nodes); atomicAdd(&gcnt->tris, cnt.tris); }
 }
 
@@ -440,9 +436,9 @@ static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const Roun
     VMN_CUDA(c, cudaMemsetAsync(qc + (cur ^ 1), 0, 4, c->stream));
     if (clk) clk->begin(ST_EXTEND);
     if (count)
-        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total);
+        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
     else
-        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total);
+        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
     if (clk) { clk->end(); clk->begin(ST_SHADE); }
     k_shade<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
                                                          qc + cur, p->ray[cur ^ 1].as<float4>(), qc + (cur ^ 1), p->radiance.as<float4>(),
