@@ -1,0 +1,155 @@
+"""CPU tests (-m "not gpu"): pin the oracle restatement (oracle/liboracle.so) against the reference's OWN code compiled
+unmodified from /root/reference (oracle/_ref/libvermref.so, -O2 -ffp-contract=off). Bar: bit-exact on every output.
+
+The reference ships no tests or golden vectors, so this build IS the pin. Where oracle/_ref is absent
+(a checkout without /root/reference and without the prebuilt .so) these tests skip and tests/test_golden.py carries the
+pin through the committed vectors generated from the same build.
+"""
+import numpy as np
+import pytest
+
+import checker
+import common
+from vermilion_b200 import scenes
+
+needs_ref = pytest.mark.skipif(not checker.Ref.available("ieee"), reason="oracle/_ref/libvermref.so not built (needs /root/reference)")
+
+ROOM = (np.array([-1900, 10, -1900], np.float32), np.array([1900, 990, 1900], np.float32))
+
+
+def _scene(name):
+    if name == "cornell":
+        return scenes.cornell()
+    if name == "spheres":
+        return scenes.spheres(2, 2, 3, 150.0)
+    if name == "soup":
+        return scenes.soup(20_000, seed=1234)
+    if name == "city":
+        return scenes.city(3, 3, 4, 2024)
+    raise KeyError(name)
+
+
+def _rays(name, pos, n, seed):
+    if name == "soup":
+        a = scenes.uniform_rays(n // 2, seed=seed, lo=0.0, hi=1000.0).view(checker.RAY).reshape(-1)
+        return np.concatenate([a, common.aimed_rays(pos, n - n // 2, seed + 1)])
+    return np.concatenate([common.aimed_rays(pos, n // 2, seed, origin_box=ROOM),
+                           common.aimed_rays(pos, n - n // 2, seed + 1, spread=0.05, origin_box=ROOM)])
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["cornell", "spheres", "soup", "city"])
+def test_intersect_bit_exact(name):
+    pos, nrm, uv = _scene(name)
+    rays = _rays(name, pos, 30_000, 5)
+    a = checker.Oracle(pos, nrm, uv).intersect(rays)
+    b = checker.Ref(pos, nrm, uv).intersect(rays)
+    assert a.tobytes() == b.tobytes()
+    assert (a["tri"] != checker.MISS).mean() > 0.2
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["cornell", "spheres"])
+def test_raycast_and_occluded_bit_exact(name):
+    pos, nrm, uv = _scene(name)
+    rays = _rays(name, pos, 20_000, 9)
+    # add the reference's dead-bounce rays (NaN direction) and axis-parallel directions
+    rays = rays.copy()
+    rays["d"][::97] = np.nan
+    rays["d"][1::97] = (0.0, -1.0, 0.0)
+    orc, ref = checker.Oracle(pos, nrm, uv), checker.Ref(pos, nrm, uv)
+    a, b = orc.raycast(rays), ref.raycast(rays)
+    for f in ("P", "dist", "N", "flags", "uv", "Le"):
+        assert np.array_equal(_bits(a[f]), _bits(b[f])), f
+    assert np.array_equal(orc.occluded(rays), ref.occluded(rays))
+
+
+@needs_ref
+@pytest.mark.parametrize("mode", [checker.MODE_COMPAT, checker.MODE_FIXED])
+def test_radiance_bit_exact(mode):
+    pos, nrm, uv = _scene("spheres")
+    rays = _rays("spheres", pos, 6000, 13)
+    a, cnt = checker.Oracle(pos, nrm, uv).radiance(rays, 5, checker.RNG_MT64, mode)
+    b = checker.Ref(pos, nrm, uv).radiance(rays, 5, mode)
+    assert np.array_equal(_bits(a), _bits(b))
+    assert cnt.min() >= 1
+    if mode == checker.MODE_FIXED:
+        assert cnt.max() <= 5
+
+
+@needs_ref
+def test_radiance_with_texture_bit_exact():
+    pos, nrm, uv = _scene("cornell")
+    tex = np.random.default_rng(2).random((16, 8, 3)).astype(np.float32)
+    orc, ref = checker.Oracle(pos, nrm, uv), checker.Ref(pos, nrm, uv)
+    orc.set_texture(tex)
+    ref.set_texture(tex)
+    rays = _rays("cornell", pos, 4000, 17)
+    a, _ = orc.radiance(rays, 3, checker.RNG_MT64, checker.MODE_FIXED)
+    b = ref.radiance(rays, 3, checker.MODE_FIXED)
+    assert np.array_equal(_bits(a), _bits(b))
+
+
+@needs_ref
+def test_camera_bit_exact():
+    ref = checker.Ref(*_scene("cornell"))
+    for cs in (checker.camera_settings(648, 432, (-4000, 1600, 8000), (0, 25, 0), 6.0, (3.6, 2.4), 128),  # renderEngine.cpp:119-142
+               checker.camera_settings(512, 512, (0, 275, 1100), (10, -20, 5), 6.0, (3.6, 3.6), 16)):
+        cam = ref.camera_fields(cs)
+        assert bytes(cam) == bytes(checker.camera_fields_py(cs))
+        rng = np.random.default_rng(1)
+        for _ in range(300):
+            p = int(rng.integers(0, cs.width * cs.height))
+            sx, sy = int(rng.integers(0, 2)), int(rng.integers(0, 2))
+            jx, jy = float(np.float32(rng.random() * 0.5)), float(np.float32(rng.random() * 0.5))
+            assert checker.Oracle.camera_ray(cam, p, sx, sy, jx, jy).tobytes() == ref.camera_ray(cs, p, sx, sy, jx, jy).tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("mode", [checker.MODE_COMPAT, checker.MODE_FIXED])
+def test_render_seeded_bit_exact(mode):
+    pos, nrm, uv = _scene("cornell")
+    cs = checker.camera_settings(40, 32, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 2.88), 16)
+    ref = checker.Ref(pos, nrm, uv)
+    img, _ = checker.Oracle(pos, nrm, uv).render(ref.camera_fields(cs), mode, checker.RNG_MT64, 7)
+    img2 = ref.render_seeded(cs, mode, 7)
+    assert np.array_equal(_bits(img), _bits(img2))
+    assert img[:, :3].max() > 0
+
+
+@needs_ref
+def test_real_pathtracer_render_statistically():
+    """The reference's real PathTracer::Render (std::random_device seed, pathtracer.cpp:231) against the seeded oracle loop:
+    only a statistical match is possible. Threshold: 2x the RMSE between two independently seeded oracle runs (§8c)."""
+    pos, nrm, uv = _scene("cornell")
+    cs = checker.camera_settings(48, 48, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 3.6), 64)
+    ref = checker.Ref(pos, nrm, uv)
+    cam = ref.camera_fields(cs)
+    real, _ = ref.render_pathtracer(cs)
+    orc = checker.Oracle(pos, nrm, uv)
+    a, _ = orc.render(cam, checker.MODE_COMPAT, checker.RNG_MT64, 1)
+    b, _ = orc.render(cam, checker.MODE_COMPAT, checker.RNG_MT64, 2)
+    floor = float(np.sqrt(np.mean((a[:, :3] - b[:, :3]) ** 2)))
+    rmse = float(np.sqrt(np.mean((real[:, :3] - a[:, :3]) ** 2)))
+    assert rmse <= 2.0 * floor + 1e-6, (rmse, floor)
+    assert abs(real[:, 4].mean() - a[:, 4].mean()) < 0.1 * a[:, 4].mean()  # samples taken per pixel (early-out)
+
+
+@needs_ref
+def test_ofast_variant_is_within_the_stated_tolerance():
+    """-Ofast (as shipped, CMakeLists.txt:20) against the IEEE oracle: ids equal except ties, t within 1e-3 relative (§8c)."""
+    if not checker.Ref.available("ofast"):
+        pytest.skip("ofast variant not built")
+    pos, nrm, uv = _scene("soup")
+    rays = _rays("soup", pos, 30_000, 23)
+    a = checker.Ref(pos, nrm, uv, variant="ieee", mesh_engine=False).intersect(rays)
+    b = checker.Ref(pos, nrm, uv, variant="ofast", mesh_engine=False).intersect(rays)
+    same = a["tri"] == b["tri"]
+    assert (~same).sum() <= 10
+    hit = same & (a["tri"] != checker.MISS)
+    rel = np.abs(a["t"][hit] - b["t"][hit]) / np.maximum(1.0, np.abs(a["t"][hit]))
+    assert rel.max() < 1e-3 and np.quantile(rel, 0.999) < 1e-5
