@@ -9,6 +9,15 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 
+def _alias_golden_generator():
+    """tests/golden/make_golden.py's scene()/rays_for() under the module name tests_golden_scenes"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("tests_golden_scenes", os.path.join(ROOT, "tests", "golden", "make_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["tests_golden_scenes"] = mod
+    spec.loader.exec_module(mod)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
@@ -21,3 +30,4 @@ def _built():
     if not all(os.path.exists(p) for p in need):
         import __graft_entry__
         __graft_entry__.build()
+    _alias_golden_generator()

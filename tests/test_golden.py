@@ -1,0 +1,99 @@
+"""Golden vectors generated from the reference's own compiled code (tests/golden/make_golden.py, run where /root/reference
+exists). CPU half: the oracle restatement reproduces them bit-exactly. GPU half (-m gpu): the CUDA path through the C ABI
+reproduces them (triangle ids exact except reported ties, everything else bit-exact where the id agrees)."""
+import os
+
+import numpy as np
+import pytest
+
+import checker
+import common
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return np.load(os.path.join(GOLD, f"{name}.npz"))
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def _cam(g, cname):
+    cam = checker.OrcCamera.from_buffer_copy(g[f"cam_{cname}_fields"].tobytes())
+    return cam
+
+
+@pytest.mark.parametrize("name", ["cornell", "spheres", "soup"])
+def test_scene_generators_unchanged(name):
+    from tests_golden_scenes import scene  # noqa: F401  (see conftest: adds tests/golden to sys.path under this alias)
+    g = load(name)
+    pos, nrm, uv = scene(name)
+    assert np.array_equal(pos, g["pos"]) and np.array_equal(nrm, g["nrm"]) and np.array_equal(uv, g["uv"])
+
+
+@pytest.mark.parametrize("name", ["cornell", "spheres", "soup"])
+def test_oracle_reproduces_golden_hits(name):
+    g = load(name)
+    orc = checker.Oracle(g["pos"], g["nrm"], g["uv"])
+    assert orc.intersect(g["rays"]).tobytes() == g["hits"].tobytes()
+    if name != "soup":
+        rc = orc.raycast(g["rays"])
+        for f in ("P", "dist", "N", "flags", "uv", "Le"):
+            assert np.array_equal(_bits(rc[f]), _bits(g["raycast"][f])), f
+        assert np.array_equal(orc.occluded(g["rays"]), g["occluded"])
+        for mode, key in ((checker.MODE_COMPAT, "radiance_compat_mt64_seed5"), (checker.MODE_FIXED, "radiance_fixed_mt64_seed5")):
+            out, _ = orc.radiance(g["rays"][:1500], 5, checker.RNG_MT64, mode)
+            assert np.array_equal(_bits(out), _bits(g[key])), key
+
+
+def test_oracle_reproduces_golden_camera_and_images():
+    g = load("cornell")
+    orc = checker.Oracle(g["pos"], g["nrm"], g["uv"])
+    for cname in ("default", "cornell"):
+        cam = _cam(g, cname)
+        px, sx, sy, jx, jy = (g[f"cam_{cname}_{k}"] for k in ("px", "sx", "sy", "jx", "jy"))
+        got = np.concatenate([checker.Oracle.camera_ray(cam, int(px[i]), int(sx[i]), int(sy[i]), float(jx[i]), float(jy[i])) for i in range(len(px))])
+        assert got.tobytes() == g[f"cam_{cname}_rays"].tobytes()
+    cam = _cam(g, "cornell")
+    for mode, key in ((checker.MODE_COMPAT, "render_compat_mt64_seed7"), (checker.MODE_FIXED, "render_fixed_mt64_seed7")):
+        img, _ = orc.render(cam, mode, checker.RNG_MT64, 7)
+        assert np.array_equal(_bits(img), _bits(g[key])), key
+
+
+# ---- GPU half -------------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cornell", "spheres", "soup"])
+def test_gpu_reproduces_golden(name):
+    from vermilion_b200 import engine
+    g = load(name)
+    with engine.Engine(device=0) as eng:
+        eng.set_scene(g["pos"], g["nrm"], g["uv"])
+        rays = g["rays"]
+        c = common.classify_hits(eng.intersect(rays), g["hits"])
+        assert c["bad"] == 0 and c["tie"] + c["edge"] <= 3, c
+        assert c["t_exact"] == c["hits"] and c["uv_err_max"] == 0.0, c
+        if name == "soup":
+            return
+        rc = eng.raycast(rays)
+        ok = ~np.isnan(rays["d"][:, 0])
+        same = (rc["tri"] == g["hits"]["tri"]) & ok
+        assert same.sum() >= ok.sum() - 3
+        for f in ("P", "dist", "N", "flags", "uv", "Le"):
+            assert np.array_equal(_bits(rc[f][same]), _bits(g["raycast"][f][same])), f
+        assert (rc["flags"][~ok] == g["raycast"]["flags"][~ok]).all()
+        assert (eng.occluded(rays) != g["occluded"]).sum() <= 3
+
+
+@pytest.mark.gpu
+def test_gpu_reproduces_golden_camera_rays():
+    from vermilion_b200 import engine
+    g = load("cornell")
+    with engine.Engine(device=0) as eng:
+        for cname in ("default", "cornell"):
+            oc = _cam(g, cname)
+            cam = engine.Camera.from_buffer_copy(bytes(oc))
+            eng.set_camera(cam)
+            got = eng.camera_rays(*(g[f"cam_{cname}_{k}"] for k in ("px", "sx", "sy", "jx", "jy")))
+            assert got.tobytes() == g[f"cam_{cname}_rays"].tobytes()

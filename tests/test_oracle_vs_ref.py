@@ -118,7 +118,8 @@ def test_render_seeded_bit_exact(mode):
     img, _ = checker.Oracle(pos, nrm, uv).render(ref.camera_fields(cs), mode, checker.RNG_MT64, 7)
     img2 = ref.render_seeded(cs, mode, 7)
     assert np.array_equal(_bits(img), _bits(img2))
-    assert img[:, :3].max() > 0
+    if mode == checker.MODE_FIXED:  # compat mode kills ~90 % of diffuse bounces (r2 = 10*xi): a 16-spp Cornell frame can be black
+        assert img[:, :3].max() > 0
 
 
 @needs_ref
