@@ -1,0 +1,55 @@
+/*
+ * adapter_harness.cpp — TEST INFRASTRUCTURE. Drives the product's reference-side binding
+ * (vermilion_b200/host/b200_pathtracer.cpp, class Vermilion::B200PathTracer : Vermilion::Integrator) the way the
+ * reference's RenderEngine::draw() does (core/engines/renderEngine.cpp:147-166): a reference Camera built by the
+ * reference constructor, a reference MeshEngine holding the scene, and a call through the Integrator vtable.
+ * Linked into oracle/_ref/libvermadapter.so together with the adapter; MeshEngine / Camera come from libvermref.so
+ * (the reference's unmodified sources), the GPU work from libvermilion_b200.so.
+ */
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "b200_pathtracer.h"
+
+struct ref_scene;
+struct ref_camera_settings {
+    uint32_t width, height;
+    float position[3];
+    float rotation_deg[3];
+    float back_distance, back_size_x, back_size_y;
+    uint32_t rays_per_pixel;
+};
+extern "C" void* ref_scene_mesh_engine(ref_scene*);
+
+extern "C" int adapter_render(ref_scene* scene, const ref_camera_settings* s, int render_mode, int mode, uint64_t seed, uint32_t max_segments,
+                              float* image, uint64_t* rays_traced, char* err, int errlen) {
+    Vermilion::cameraSettings vcs;
+    vcs.imageResX = s->width; vcs.imageResY = s->height;
+    vcs.position = Vermilion::float3(s->position[0], s->position[1], s->position[2]);
+    vcs.rotation = Vermilion::float3(s->rotation_deg[0], s->rotation_deg[1], s->rotation_deg[2]);
+    vcs.fBackDistance = s->back_distance;
+    vcs.horAngleOfView = 90.f;
+    vcs.raysPerPixel = s->rays_per_pixel;
+    vcs.fBackSizeX = s->back_size_x; vcs.fBackSizeY = s->back_size_y;
+    vcs.rayMaxBounces = 5; vcs.tileSize = 16;
+    vcs.renderMode = (Vermilion::vermRenderMode)render_mode;
+    Vermilion::Camera* cam = new Vermilion::Camera(vcs);
+    std::vector<Vermilion::Camera*> cams{cam};
+
+    Vermilion::B200Options opt;
+    opt.mode = mode; opt.seed = seed; opt.maxSegments = max_segments;
+    Vermilion::B200PathTracer* b200 = new Vermilion::B200PathTracer(opt);
+    Vermilion::Integrator* integrator = b200; // main.cpp:60-63
+    integrator->Render(cams, static_cast<Vermilion::MeshEngine*>(ref_scene_mesh_engine(scene)));
+    int rc = b200->ok() ? 0 : 1;
+    if (err && errlen > 0) { strncpy(err, b200->lastError().c_str(), errlen - 1); err[errlen - 1] = 0; }
+    if (rays_traced) *rays_traced = b200->stats().rays_traced;
+    size_t per = render_mode == (int)Vermilion::vermRenderMode::RGBAZ ? 5 : render_mode == (int)Vermilion::vermRenderMode::RGBA ? 4
+               : render_mode == (int)Vermilion::vermRenderMode::RGB ? 3 : 1;
+    if (rc == 0) memcpy(image, cam->mImage, sizeof(float) * per * (size_t)cam->RenderTargetSize);
+    delete integrator;
+    delete cam;
+    return rc;
+}

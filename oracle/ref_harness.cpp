@@ -395,6 +395,9 @@ void ref_render_seeded(const ref_scene* s, const ref_camera_settings* cs, int mo
     delete cam;
 }
 
+/* the reference MeshEngine of a scene, for oracle/adapter_harness.cpp (the Integrator adapter under test) */
+void* ref_scene_mesh_engine(ref_scene* s) { return s ? s->mesh : nullptr; }
+
 const char* ref_build_flags(void) {
 #ifdef VERMREF_FLAGS
     return VERMREF_FLAGS;

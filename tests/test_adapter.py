@@ -1,0 +1,67 @@
+"""The drop-in seam: Vermilion::B200PathTracer (vermilion_b200/host/b200_pathtracer.cpp) called through the reference's own
+Integrator vtable with a reference Camera and a reference MeshEngine (oracle/_ref/libvermadapter.so, built from the reference
+headers/objects where /root/reference exists; the prebuilt .so travels to the GPU box)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import checker
+from vermilion_b200 import scenes
+
+ADAPTER = os.path.join(checker.ORACLE_DIR, "_ref", "libvermadapter.so")
+needs_adapter = pytest.mark.skipif(not (os.path.exists(ADAPTER) and checker.Ref.available("ieee")), reason="oracle/_ref/libvermadapter.so not built")
+RGB, RGBA, RGBAZ = 0, 1, 2  # vermRenderMode (camera.h:21-30)
+
+
+def adapter_render(ref, cs, render_mode, mode, seed, max_segments=5):
+    L = C.CDLL(ADAPTER)
+    L.adapter_render.argtypes = [C.c_void_p, C.POINTER(checker.RefCameraSettings), C.c_int, C.c_int, C.c_uint64, C.c_uint32, C.c_void_p,
+                                 C.POINTER(C.c_uint64), C.c_char_p, C.c_int]
+    per = {RGB: 3, RGBA: 4, RGBAZ: 5}[render_mode]
+    img = np.zeros((cs.width * cs.height, per), np.float32)
+    rays = C.c_uint64()
+    err = C.create_string_buffer(512)
+    rc = L.adapter_render(ref.h, C.byref(cs), render_mode, mode, seed, max_segments, img.ctypes.data_as(C.c_void_p), C.byref(rays), err, 512)
+    return rc, img, rays.value, err.value.decode()
+
+
+@needs_adapter
+def test_adapter_fails_loudly_without_a_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    pos, nrm, uv = scenes.cornell()
+    ref = checker.Ref(pos, nrm, uv)
+    cs = checker.camera_settings(16, 16, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 3.6), 16)
+    rc, img, _, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 3)
+    assert rc != 0 and "CUDA" in err
+    assert not img.any()  # film untouched: nothing was rendered on the CPU instead
+
+
+@pytest.mark.gpu
+@needs_adapter
+@pytest.mark.parametrize("mode", [checker.MODE_COMPAT, checker.MODE_FIXED])
+def test_adapter_matches_oracle_through_the_integrator_interface(mode):
+    from vermilion_b200 import engine
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    ref = checker.Ref(pos, nrm, uv)
+    cs = checker.camera_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16)
+    rc, img, nrays, err = adapter_render(ref, cs, RGBAZ, mode, 11)
+    assert rc == 0, err
+    # the same frame through the plain C ABI: identical bits
+    with engine.Engine(device=0) as eng:
+        eng.set_scene(pos, nrm, uv)
+        eng.set_camera(engine.camera_from_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16))
+        eng.render(mode=mode, seed=11)
+        direct = eng.read_image()
+    assert np.array_equal(img.view(np.uint32), direct.view(np.uint32))
+    # and against the CPU oracle with the shared Philox stream
+    oimg, onrays = checker.Oracle(pos, nrm, uv).render(ref.camera_fields(cs), mode, checker.RNG_PHILOX, 11)
+    assert np.array_equal(img[:, 3:], oimg[:, 3:])
+    assert (img[:, :3].view(np.uint32) == oimg[:, :3].view(np.uint32)).all(1).mean() > 0.97
+    assert abs(nrays - onrays) <= 0.002 * onrays
+    # other film layouts go through Camera::setPixelValue (camera.cpp:88-124)
+    rc, rgb, _, err = adapter_render(ref, cs, RGB, mode, 11)
+    assert rc == 0 and np.array_equal(rgb, img[:, :3])

@@ -1,0 +1,134 @@
+// b200_pathtracer.cpp — Vermilion::B200PathTracer, see b200_pathtracer.h.
+//
+// Replaces PathTracer::Render (reference core/integrators/pathtracer.cpp:200-328) with calls into the C ABI:
+//   geometry  : MeshEngine::sceneMeshes walked exactly as MeshEngine::createBVH does (core/engines/meshEngine.cpp:660-717),
+//               which defines the canonical triangle order; uv only when the mesh HasTextureCoords(0)
+//   spheres   : the eight analytic spheres hard-coded in MeshEngine::RayCast (meshEngine.cpp:377-500) via vmn_reference_spheres
+//   texture   : MeshEngine::boundTextures[0], the only one Radiance samples (pathtracer.cpp:62-80)
+//   camera    : the public Camera fields the pixel loop reads (core/camera/camera.h:66-104)
+//   film      : written back into Camera::mImage in the layout of Camera::renderMode (camera.cpp:88-124)
+#include "b200_pathtracer.h"
+
+#include <cstdio>
+#include <cstring>
+
+namespace Vermilion
+{
+
+B200PathTracer::B200PathTracer(const B200Options& options) : mOpt(options)
+{
+    vmn_config cfg{};
+    cfg.device = mOpt.device;
+    cfg.max_paths = mOpt.maxPathsInFlight;
+    mLastStatus = vmn_create(&cfg, &mCtx);
+    if (mLastStatus != VMN_OK)
+    {
+        mLastError = mCtx ? vmn_last_error(mCtx) : "vmn_create: out of memory";
+        fprintf(stderr, "[B200PathTracer] cannot create the GPU engine: %s\n", mLastError.c_str());
+        if (mCtx) vmn_destroy(mCtx);
+        mCtx = nullptr;
+    }
+}
+
+B200PathTracer::~B200PathTracer()
+{
+    if (mCtx) vmn_destroy(mCtx);
+}
+
+bool B200PathTracer::fail(const char* what)
+{
+    mLastError = std::string(what) + ": " + (mCtx ? vmn_last_error(mCtx) : "no context");
+    fprintf(stderr, "[B200PathTracer] %s\n", mLastError.c_str());
+    return false;
+}
+
+bool B200PathTracer::uploadScene(MeshEngine* mEng)
+{
+    uint64_t nFaces = 0;
+    for (aiMesh* mesh : mEng->sceneMeshes) nFaces += mesh->mNumFaces;
+    if (mSceneKey == mEng && mSceneFaces == nFaces && mSceneTextures == mEng->boundTextures.size()) return true;
+
+    std::vector<float> pos(9 * nFaces), nrm(9 * nFaces), uv(6 * nFaces, 0.f);
+    uint64_t f = 0;
+    for (aiMesh* mesh : mEng->sceneMeshes)
+    {
+        const bool hasUV = mesh->HasTextureCoords(0);
+        for (uint32_t i = 0; i < mesh->mNumFaces; ++i, ++f)
+        {
+            for (int k = 0; k < 3; ++k)
+            {
+                const unsigned idx = mesh->mFaces[i].mIndices[k];
+                pos[9 * f + 3 * k + 0] = mesh->mVertices[idx].x;
+                pos[9 * f + 3 * k + 1] = mesh->mVertices[idx].y;
+                pos[9 * f + 3 * k + 2] = mesh->mVertices[idx].z;
+                nrm[9 * f + 3 * k + 0] = mesh->mNormals[idx].x;
+                nrm[9 * f + 3 * k + 1] = mesh->mNormals[idx].y;
+                nrm[9 * f + 3 * k + 2] = mesh->mNormals[idx].z;
+                if (hasUV)
+                {
+                    uv[6 * f + 2 * k + 0] = mesh->mTextureCoords[0][idx].x;
+                    uv[6 * f + 2 * k + 1] = mesh->mTextureCoords[0][idx].y;
+                }
+            }
+        }
+    }
+    if ((mLastStatus = vmn_scene_set_triangles(mCtx, pos.data(), nrm.data(), uv.data(), nFaces)) != VMN_OK) return fail("vmn_scene_set_triangles");
+    vmn_sphere spheres[8];
+    vmn_reference_spheres(spheres);
+    if ((mLastStatus = vmn_scene_set_spheres(mCtx, spheres, 8)) != VMN_OK) return fail("vmn_scene_set_spheres");
+    if (!mEng->boundTextures.empty())
+    {
+        const VermiTexture& t = mEng->boundTextures[0];
+        if ((mLastStatus = vmn_scene_set_texture(mCtx, 0, t.pData, t.nWidth, t.nHeight, t.nChannels)) != VMN_OK) return fail("vmn_scene_set_texture");
+    }
+    if ((mLastStatus = vmn_scene_commit(mCtx)) != VMN_OK) return fail("vmn_scene_commit");
+    mSceneKey = mEng; mSceneFaces = nFaces; mSceneTextures = mEng->boundTextures.size();
+    return true;
+}
+
+void B200PathTracer::Render(std::vector<Vermilion::Camera*>& cameraList, MeshEngine* mEng)
+{
+    if (!mCtx) { fprintf(stderr, "[B200PathTracer] no GPU engine (there is no CPU fallback); frame not rendered\n"); return; }
+    if (!mEng) { mLastStatus = VMN_ERR_INVALID; mLastError = "null MeshEngine"; return; }
+    if (!uploadScene(mEng)) return;
+
+    for (Vermilion::Camera* cam : cameraList) // pathtracer.cpp:210
+    {
+        vmn_camera vc{};
+        vc.width = cam->uImageU; vc.height = cam->uImageV;
+        for (int i = 0; i < 3; ++i) { vc.position[i] = cam->mPosition[i]; vc.rotation[i] = cam->mRotation[i]; }
+        vc.dist_to_film = cam->mDistToFilm;
+        vc.sensor_x = cam->sensorSizeX; vc.sensor_y = cam->sensorSizeY;
+        vc.spp = cam->uSamplesPerPixel;
+        if ((mLastStatus = vmn_camera_set(mCtx, &vc)) != VMN_OK) { fail("vmn_camera_set"); return; }
+
+        vmn_render_params rp{};
+        rp.mode = mOpt.mode; rp.max_segments = mOpt.maxSegments; rp.seed = mOpt.seed;
+        rp.tile_size = mOpt.tileSize; rp.tile_rank = mOpt.tileRank; rp.tile_world = mOpt.tileWorld;
+        rp.sample_begin = mOpt.sampleBegin; rp.sample_end = mOpt.sampleEnd;
+        if ((mLastStatus = vmn_render(mCtx, &rp)) != VMN_OK) { fail("vmn_render"); return; }
+        vmn_get_stats(mCtx, &mStats);
+
+        const uint64_t npix = (uint64_t)vc.width * vc.height;
+        if (cam->renderMode == vermRenderMode::RGBAZ)
+        {
+            // Camera::mImage already has the RGBAZ layout (camera.cpp:106-113): bulk write
+            if ((mLastStatus = vmn_read_image(mCtx, cam->mImage, VMN_FILM_RGBAZ)) != VMN_OK) { fail("vmn_read_image"); return; }
+        }
+        else
+        {
+            std::vector<float> img(5 * npix);
+            if ((mLastStatus = vmn_read_image(mCtx, img.data(), VMN_FILM_RGBAZ)) != VMN_OK) { fail("vmn_read_image"); return; }
+            for (uint64_t p = 0; p < npix; ++p) // pathtracer.cpp:318-324
+            {
+                pixelValue px;
+                px.pixel = p;
+                px.red = img[5 * p]; px.green = img[5 * p + 1]; px.blue = img[5 * p + 2]; px.alpha = img[5 * p + 3]; px.depth = img[5 * p + 4];
+                px.light = 0.f;
+                cam->setPixelValue(px); // throws std::exception for unsupported modes, as the reference does (camera.cpp:122)
+            }
+        }
+    }
+}
+
+}

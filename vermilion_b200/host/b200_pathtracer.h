@@ -1,0 +1,65 @@
+// b200_pathtracer.h — the reference-side binding of libvermilion_b200.so: a Vermilion::Integrator.
+//
+// Drop-in for `new PathTracer()` in the reference's main.cpp:60-63:
+//
+//     Vermilion::Integrator* integrator = new Vermilion::B200PathTracer();   // was: new Vermilion::PathTracer()
+//     rEng->assignIntegrator(integrator);                                    // renderEngine.cpp:70-78
+//     ...
+//     rEng->draw();                                                          // -> integrator->Render(mCameras, mMeshEngine)
+//
+// It is compiled against the reference's own headers (core/integrators/integrators.h, core/camera/camera.h,
+// core/engines/meshEngine.h) and links only the C ABI in include/vermilion_b200.h — no CUDA headers, no CPU fallback:
+// when the GPU engine cannot be created Render() logs the error and leaves the film untouched (the reference's
+// Render returns void and reports failures through its logs, renderEngine.cpp:150-154).
+#ifndef VERMILION_B200_PATHTRACER_H
+#define VERMILION_B200_PATHTRACER_H
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "integrators/integrators.h"
+#include "engines/meshEngine.h"
+#include "vermilion_b200.h"
+
+namespace Vermilion
+{
+    struct B200Options
+    {
+        int device = 0;
+        int mode = VMN_MODE_COMPAT;      // the reference estimator; VMN_MODE_FIXED = exact spp, r2 = xi, <= maxSegments rays per path
+        uint32_t maxSegments = 5;
+        uint64_t seed = 1;               // the reference seeds from std::random_device (pathtracer.cpp:231); here it is explicit
+        uint64_t maxPathsInFlight = 0;   // 0 = library default
+        // multi-GPU share of the frame (one process per GPU; the caller all-reduces the film)
+        uint32_t tileSize = 0, tileRank = 0, tileWorld = 1;
+        uint32_t sampleBegin = 0, sampleEnd = 0;
+    };
+
+    class B200PathTracer : public Integrator
+    {
+    public:
+        explicit B200PathTracer(const B200Options& options = B200Options());
+        ~B200PathTracer() override;
+        void Render(std::vector<Vermilion::Camera*>& cameraList, MeshEngine* mEng) override;
+
+        bool ok() const { return mCtx != nullptr && mLastStatus == VMN_OK; }
+        const std::string& lastError() const { return mLastError; }
+        const vmn_stats& stats() const { return mStats; }
+        vmn_ctx* context() { return mCtx; }
+
+    private:
+        bool uploadScene(MeshEngine* mEng);
+        bool fail(const char* what);
+
+        B200Options mOpt;
+        vmn_ctx* mCtx = nullptr;
+        vmn_status mLastStatus = VMN_OK;
+        std::string mLastError;
+        vmn_stats mStats{};
+        // scene cache key: re-upload only when the MeshEngine's geometry changed
+        const void* mSceneKey = nullptr;
+        uint64_t mSceneFaces = 0;
+        size_t mSceneTextures = 0;
+    };
+}
+#endif
