@@ -89,10 +89,18 @@ class ClockSampler:
 
 
 # ---- CPU reference arm ----------------------------------------------------------------------------------------
-def cpu_reference_sample(pos, nrm, uv, width, height, spp, budget_s=20.0, threads=0):
+def _bit_reversed(n):
+    """0..n-1 in bit-reversed order: any prefix of it is spread evenly over the range."""
+    bits = max(1, (n - 1).bit_length())
+    order = [int(format(i, f"0{bits}b")[::-1], 2) for i in range(1 << bits)]
+    return [i for i in order if i < n]
+
+
+def cpu_reference_sample(pos, nrm, uv, width, height, spp, budget_s=12.0, threads=0, rows_per_band=8):
     """Times the reference's own CPU code (oracle/_ref/libvermref_ofast.so: unmodified Triangle/BVH/MeshEngine::RayCast, -Ofast as
-    shipped) on a bounded sample of the workload: horizontal 1-row bands spread over the frame, all `spp` samples, FIXED mode.
-    Rays are counted by the bit-identical oracle port on the same pixels (untimed). Falls back to the port if _ref is absent."""
+    shipped) on a bounded sample of the workload: 8-row bands taken in bit-reversed order (so any prefix is spread over the frame),
+    all `spp` samples, FIXED mode, until `budget_s` seconds of CPU work are spent. Rays are counted by the bit-identical oracle port on
+    the same pixels (untimed; the reference has no ray counter). Falls back to timing the port if oracle/_ref is absent."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import checker
     cs = checker.camera_settings(width, height, CAM_POS, CAM_ROT, 6.0, (3.6, 3.6 * height / width), spp)
@@ -103,10 +111,11 @@ def cpu_reference_sample(pos, nrm, uv, width, height, spp, budget_s=20.0, thread
     ref = checker.Ref(pos, nrm, uv, variant="ofast") if kind == "reference" else None
     build_s = time.time() - t_build0
     cores = checker.Oracle.max_threads() if threads <= 0 else threads
-    rows = [int((k + 0.5) * height / 16) for k in range(16)]
+    nbands = -(-height // rows_per_band)
     secs, rays, paths, used = 0.0, 0, 0, 0
-    for r in rows:
-        p0, p1 = r * width, (r + 1) * width
+    for band in _bit_reversed(nbands):
+        r0, r1 = band * rows_per_band, min(height, (band + 1) * rows_per_band)
+        p0, p1 = r0 * width, r1 * width
         t0 = time.time()
         if ref is not None:
             ref.render_seeded(cs, mode=checker.MODE_FIXED, seed=1, p0=p0, p1=p1, s0=0, s1=spp, max_segments=5, threads=threads)
@@ -115,13 +124,13 @@ def cpu_reference_sample(pos, nrm, uv, width, height, spp, budget_s=20.0, thread
         secs += time.time() - t0
         _, n = orc.render(ocam, checker.MODE_FIXED, checker.RNG_MT64, 1, p0, p1, 0, spp, 5, 0)
         rays += n
-        paths += width * spp
+        paths += (p1 - p0) * spp
         used += 1
         if secs > budget_s:
             break
     return {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
-            "sample": f"{used} one-pixel-high rows spread over the {width}x{height} frame, all {spp} spp, FIXED mode: {paths} paths, {rays} rays in "
-                      f"{secs:.1f} s (reference BVH build {build_s:.1f} s not included)",
+            "sample": f"{used} of {nbands} {rows_per_band}-row bands (bit-reversed order, spread over the {width}x{height} frame), all {spp} spp, FIXED mode: "
+                      f"{paths} paths, {rays} rays in {secs:.1f} s of CPU time (reference BVH build {build_s:.1f} s not included)",
             "spp_per_s": paths / secs / (width * height)}
 
 
@@ -155,7 +164,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--spp", type=int, default=64)
     ap.add_argument("--res", default="1920x1080")
-    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--max-paths", type=int, default=8 << 20)
     args = ap.parse_args()
@@ -165,6 +174,7 @@ def main():
 
     import torch
     import torch.distributed as dist
+    from vermilion_b200 import distributed as vd
     from vermilion_b200 import engine
 
     rank = int(os.environ.get("RANK", "0"))
@@ -192,22 +202,16 @@ def main():
     eng.set_scene(pos, nrm, uv)
     eng.set_camera(cam)
     d_film, n_floats = eng.film_device()
-    film_t = None
-    if world > 1:
-        # torch view of the context's film buffer for the NCCL all-reduce
-        class _Ptr:
-            pass
-        holder = _Ptr()
-        holder.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (d_film, False), "version": 3}
-        film_t = torch.as_tensor(holder, device=torch.device("cuda", local))
+    film_t = vd.device_film_tensor(eng, torch.device("cuda", local)) if world > 1 else None
 
-    s0, s1 = rank * args.spp, (rank + 1) * args.spp
+    share = vd.render_params("sample", rank, world, spp_total)  # this rank's slice of the sample sequence
+    s0, s1 = share["sample_begin"], share["sample_end"]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def step():
         eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
         if world > 1:
-            dist.all_reduce(film_t)
+            vd.reduce_film(film_t)
 
     def barrier():
         torch.cuda.synchronize()
@@ -253,7 +257,7 @@ def main():
         eng.set_camera(cam)
         eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
         if world > 1:
-            dist.all_reduce(film_t)
+            vd.reduce_film(film_t)
             img = eng.resolve_device(d_film)
         else:
             img = eng.read_image()
@@ -289,11 +293,19 @@ def main():
     peak, peak_src = peaks()
     achieved = (rays / max(1e-9, extend_ms / 1e3)) * b_ray / 1e9
     n_extend = args.steps * 5 * -(-(npix * args.spp) // (args.max_paths // npix * npix if args.max_paths >= npix else args.max_paths))
-    roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per k_extend launch, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f)["k_extend"]["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": peak_src, "bytes_per_ray": b_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                 "node_bytes": cst["node_bytes"], "tri_bytes": cst["tri_bytes"], "extend_ms_per_step": extend_ms / args.steps,
                 "extend_share_of_step": extend_ms / ms if world == 1 else None, "extend_launches": int(n_extend),
-                "note": "algorithmic bytes; the 52 MB scene is L2-resident on this config, so achieved can exceed the HBM copy peak"}
+                "algorithmic_bytes_per_launch": b_ray * rays / max(1, n_extend),
+                "note": "algorithmic bytes (SURVEY 8d B_ray); on C2 the ~60 MB of nodes+triangles stay L2-resident, so measured DRAM traffic is far below "
+                        "the algorithmic bytes and the kernel is issue-bound (profiles/); tools/microbench_c3.py is the HBM-bound row"}
 
     cpu = None
     if not args.no_cpu and world == 1:

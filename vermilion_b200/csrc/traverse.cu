@@ -10,6 +10,9 @@
 namespace vmn {
 
 constexpr int kTraceBlock = 128;
+#ifndef VMN_TRACE_MINB
+#define VMN_TRACE_MINB 8 // 64 registers: 8 resident CTAs per SM measured fastest (22.3 ms vs 26.7 ms at 96 registers on C2)
+#endif
 
 __device__ __forceinline__ bool claim_rays(unsigned long long* next, uint64_t n, uint64_t* i_out) {
     unsigned long long base = 0;
@@ -38,10 +41,11 @@ __device__ __forceinline__ uint32_t closest_hit(const SceneDev& sc, V3 o, V3 d, 
 }
 
 template <bool WIDE, bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
+__global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
                                                            vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt,
                                                            uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
     auto finish = [&](uint64_t i, V3 o, V3 d, float t, uint32_t k, const TriRec* base) {
@@ -55,7 +59,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect(SceneDev sc, const vm
         reinterpret_cast<float4*>(out)[i] = make_float4(t, u, v, __uint_as_float(id));
     };
     if (WIDE) {
-        persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, &cnt,
+        persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
                                 [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
                                 [&](uint64_t i, const Trav& s) { finish(i, s.o, s.d, s.best_t, s.best, sc.tris); });
     } else {
@@ -75,39 +79,37 @@ __global__ void __launch_bounds__(kTraceBlock) k_intersect(SceneDev sc, const vm
     }
 }
 
-__global__ void __launch_bounds__(kTraceBlock) k_occluded(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n, uint8_t* __restrict__ out,
-                                                          unsigned long long* next) {
-    __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
-    uint2* sstack = sstack_all + threadIdx.x;
-    uint64_t i;
-    while (claim_rays(next, n, &i)) {
-        if (i >= n) continue;
-        V3 o, d;
-        load_ray(rays, i, &o, &d);
-        float t;
-        const uint32_t id = closest_hit<true, false>(sc, o, d, &t, sstack, nullptr);
-        out[i] = (id != VMN_MISS && (double)t > 1e-3) ? 1 : 0; // meshEngine.cpp:196-207
-    }
+__device__ __forceinline__ uint32_t original_id(const SceneDev& sc, uint32_t k) {
+    return k == VMN_MISS ? VMN_MISS : __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + k)->w));
 }
 
-__global__ void __launch_bounds__(kTraceBlock) k_raycast(SceneDev sc, const SphereDev* __restrict__ sph, const vmn_ray* __restrict__ rays, uint64_t n,
-                                                         vmn_raycast_rec* __restrict__ out, unsigned long long* next) {
+__global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_occluded(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n, uint8_t* __restrict__ out,
+                                                          unsigned long long* next, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
-    uint64_t i;
-    while (claim_rays(next, n, &i)) {
-        if (i >= n) continue;
-        V3 o, d;
-        load_ray(rays, i, &o, &d);
-        float t;
-        const uint32_t id = closest_hit<true, false>(sc, o, d, &t, sstack, nullptr);
-        const RayCastOut r = raycast_finish(sc, sph, o, d, t, id);
-        float4* q = reinterpret_cast<float4*>(out + i);
-        q[0] = make_float4(r.P.x, r.P.y, r.P.z, r.dist);
-        q[1] = make_float4(r.N.x, r.N.y, r.N.z, __uint_as_float((r.hit ? VMN_RC_HIT : 0u) | (r.material ? VMN_RC_MATERIAL : 0u)));
-        q[2] = make_float4(r.uv0, r.uv1, r.Le.x, r.Le.y);
-        q[3] = make_float4(r.Le.z, __uint_as_float(r.tri), 0.f, 0.f);
-    }
+    TravCounters cnt{0ull, 0ull};
+    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+                            [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
+                            [&](uint64_t i, const Trav& s) { out[i] = (s.best != VMN_MISS && (double)s.best_t > 1e-3) ? 1 : 0; }); // meshEngine.cpp:196-207
+}
+
+__global__ void __launch_bounds__(kTraceBlock, 6) k_raycast(SceneDev sc, const SphereDev* __restrict__ sph, const vmn_ray* __restrict__ rays, uint64_t n,
+                                                         vmn_raycast_rec* __restrict__ out, unsigned long long* next, uint32_t refill_min) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
+    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
+    uint2* sstack = sstack_all + threadIdx.x;
+    TravCounters cnt{0ull, 0ull};
+    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+                            [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
+                            [&](uint64_t i, const Trav& s) {
+                                const RayCastOut r = raycast_finish(sc, sph, s.o, s.d, s.best_t, original_id(sc, s.best));
+                                float4* q = reinterpret_cast<float4*>(out + i);
+                                q[0] = make_float4(r.P.x, r.P.y, r.P.z, r.dist);
+                                q[1] = make_float4(r.N.x, r.N.y, r.N.z, __uint_as_float((r.hit ? VMN_RC_HIT : 0u) | (r.material ? VMN_RC_MATERIAL : 0u)));
+                                q[2] = make_float4(r.uv0, r.uv1, r.Le.x, r.Le.y);
+                                q[3] = make_float4(r.Le.z, __uint_as_float(r.tri), 0.f, 0.f);
+                            });
 }
 
 template <class K>
@@ -156,7 +158,7 @@ vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_
     vmn_status s = reset_counters(c);
     if (s != VMN_OK) return s;
     if (n) {
-        k_occluded<<<resident_grid(c, k_occluded), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, c->counters.as<unsigned long long>());
+        k_occluded<<<resident_grid(c, k_occluded), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, c->counters.as<unsigned long long>(), refill_min());
         VMN_CUDA(c, cudaGetLastError());
     }
     c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;
@@ -168,7 +170,7 @@ vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_ray
     if (s != VMN_OK) return s;
     if (n) {
         k_raycast<<<resident_grid(c, k_raycast), kTraceBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), d_rays, n, d_out,
-                                                                            c->counters.as<unsigned long long>());
+                                                                            c->counters.as<unsigned long long>(), refill_min());
         VMN_CUDA(c, cudaGetLastError());
     }
     c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;

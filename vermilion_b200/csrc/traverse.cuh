@@ -18,6 +18,12 @@ namespace vmn {
 #define VMN_T_MISS 999999999.f // bvh.cpp:48
 #define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
 #define VMN_LOCAL_STACK 52     // overflow entries in local memory
+#ifndef VMN_SPH_UNROLL
+#define VMN_SPH_UNROLL 0
+#endif
+#ifndef VMN_COOP
+#define VMN_COOP 1            // warp-pooled triangle tests (trav_tris_coop); 0 = per-lane loop
+#endif
 
 struct TravCounters { unsigned long long nodes, tris; };
 
@@ -69,11 +75,13 @@ struct Trav {
     uint32_t best;  // index into sc.tris
 };
 
-// quantised byte j of word w as an exact float: PRMT builds 0x4B0000qq = 2^23 + q, one FADD removes the bias.
-// (I2F.U8 runs on the quarter-rate XU pipe and was 33 % of all stall samples in the first profile.)
+// Quantised byte J of word w as the float 1 + q * 2^-15: one PRMT builds 0x3F80qq00 (q in mantissa bits 8..15). The plane
+// distance q*a + b is then evaluated as fma(1 + q*2^-15, a*2^15, b - a*2^15): one PRMT + one FFMA per plane. (I2F.U8 runs on the
+// quarter-rate XU pipe and was 33 % of all stall samples in the first profile; the 2^23-bias form needed an extra FADD per plane.)
+// Rounding of b - a*2^15 costs at most 2^-9 of a quantisation cell; trav_node() widens every slab by 2^-8 cell to stay conservative.
 template <int J>
-__device__ __forceinline__ float byte_to_float(uint32_t w) {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | J)) - 8388608.0f;
+__device__ __forceinline__ float byte_to_unit(uint32_t w) {
+    return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | (J << 4)));
 }
 
 __device__ __forceinline__ bool trav_init(Trav& s, const SceneDev& sc, V3 o, V3 d) {
@@ -90,13 +98,14 @@ __device__ __forceinline__ bool trav_init(Trav& s, const SceneDev& sc, V3 o, V3 
 
 template <int J>
 __device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint32_t nyw, uint32_t nzw, uint32_t fxw, uint32_t fyw, uint32_t fzw,
-                                              float ax, float ay, float az, float bx, float by, float bz, float best_t, uint32_t oct_inv) {
-    const float tnx = __fmaf_rn(byte_to_float<J>(nxw), ax, bx);
-    const float tny = __fmaf_rn(byte_to_float<J>(nyw), ay, by);
-    const float tnz = __fmaf_rn(byte_to_float<J>(nzw), az, bz);
-    const float tfx = __fmaf_rn(byte_to_float<J>(fxw), ax, bx);
-    const float tfy = __fmaf_rn(byte_to_float<J>(fyw), ay, by);
-    const float tfz = __fmaf_rn(byte_to_float<J>(fzw), az, bz);
+                                              float ax, float ay, float az, float nbx, float nby, float nbz, float fbx, float fby, float fbz,
+                                              float best_t, uint32_t oct_inv) {
+    const float tnx = __fmaf_rn(byte_to_unit<J>(nxw), ax, nbx);
+    const float tny = __fmaf_rn(byte_to_unit<J>(nyw), ay, nby);
+    const float tnz = __fmaf_rn(byte_to_unit<J>(nzw), az, nbz);
+    const float tfx = __fmaf_rn(byte_to_unit<J>(fxw), ax, fbx);
+    const float tfy = __fmaf_rn(byte_to_unit<J>(fyw), ay, fby);
+    const float tfz = __fmaf_rn(byte_to_unit<J>(fzw), az, fbz);
     const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
     const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
     if (tn <= tf) {
@@ -108,10 +117,12 @@ __device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint
     return 0u;
 }
 
-// One traversal step: visit the next pending node (8 child boxes), test the triangles it exposes, pop if nothing is
-// pending. Returns false when the ray is finished.
+// A traversal step has three phases, so that the triangle tests of a whole warp can be pooled (trav_tris_coop):
+//   trav_node : visit the next pending node (8 child boxes) or turn a popped triangle group into pending triangles
+//   trav_tris : test the pending triangles
+//   trav_pop  : pop the next node group if none is pending; false when the ray is finished
 template <bool COUNT>
-__device__ __forceinline__ bool trav_step(Trav& s, const SceneDev& sc, uint2* sstack, uint32_t sstride, uint2* lstack, TravCounters* cnt) {
+__device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* sstack, uint32_t sstride, uint2* lstack, TravCounters* cnt) {
     const uint4* __restrict__ nodes = reinterpret_cast<const uint4*>(sc.nodes);
     if (s.ng.y & 0xFF000000u) {
         const uint32_t bit = 31u - __clz(s.ng.y);
@@ -126,19 +137,24 @@ __device__ __forceinline__ bool trav_step(Trav& s, const SceneDev& sc, uint2* ss
         const uint4* np = nodes + 5ull * nidx;
         const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
         if (COUNT) ++cnt->nodes;
+        // per-axis: t(q) = q * a + b with a = 2^(e-127) / d, b = (p - o) / d, evaluated as fma(1 + q*2^-15, A, B), A = a * 2^15,
+        // B = b - A, widened by |a| * 2^-8 (see byte_to_unit)
         const float ax = __uint_as_float((q0.w & 0xFFu) << 23) * s.idx;
         const float ay = __uint_as_float(((q0.w >> 8) & 0xFFu) << 23) * s.idy;
         const float az = __uint_as_float(((q0.w >> 16) & 0xFFu) << 23) * s.idz;
-        const float bx = (__uint_as_float(q0.x) - s.o.x) * s.idx;
-        const float by = (__uint_as_float(q0.y) - s.o.y) * s.idy;
-        const float bz = (__uint_as_float(q0.z) - s.o.z) * s.idz;
+        const float Ax = ax * 32768.f, Ay = ay * 32768.f, Az = az * 32768.f;
+        const float bx = (__uint_as_float(q0.x) - s.o.x) * s.idx - Ax;
+        const float by = (__uint_as_float(q0.y) - s.o.y) * s.idy - Ay;
+        const float bz = (__uint_as_float(q0.z) - s.o.z) * s.idz - Az;
+        const float mx = fabsf(ax) * 0.00390625f, my = fabsf(ay) * 0.00390625f, mz = fabsf(az) * 0.00390625f;
+        const float nbx = bx - mx, nby = by - my, nbz = bz - mz, fbx = bx + mx, fby = by + my, fbz = bz + mz;
         // near/far byte planes per axis (two words = 8 children each)
         const bool ngx = s.d.x < 0.f, ngy = s.d.y < 0.f, ngz = s.d.z < 0.f;
         const uint32_t nx0 = ngx ? q3.z : q2.x, nx1 = ngx ? q3.w : q2.y, fx0 = ngx ? q2.x : q3.z, fx1 = ngx ? q2.y : q3.w;
         const uint32_t ny0 = ngy ? q4.x : q2.z, ny1 = ngy ? q4.y : q2.w, fy0 = ngy ? q2.z : q4.x, fy1 = ngy ? q2.w : q4.y;
         const uint32_t nz0 = ngz ? q4.z : q3.x, nz1 = ngz ? q4.w : q3.y, fz0 = ngz ? q3.x : q4.z, fz1 = ngz ? q3.y : q4.w;
         uint32_t hitmask = 0;
-#define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, ax, ay, az, bx, by, bz, s.best_t, s.oct_inv)
+#define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv)
         VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
         VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
 #undef VMN_CH
@@ -148,6 +164,11 @@ __device__ __forceinline__ bool trav_step(Trav& s, const SceneDev& sc, uint2* ss
         s.tg = s.ng;
         s.ng = make_uint2(0u, 0u);
     }
+}
+
+// per-lane triangle loop (single-ray form)
+template <bool COUNT>
+__device__ __forceinline__ void trav_tris(Trav& s, const SceneDev& sc, TravCounters* cnt) {
     while (s.tg.y) {
         const uint32_t i = __ffs(s.tg.y) - 1u;
         s.tg.y &= s.tg.y - 1u;
@@ -157,12 +178,77 @@ __device__ __forceinline__ bool trav_step(Trav& s, const SceneDev& sc, uint2* ss
         float ct;
         if (tri_intersect(T, s.o, s.d, &ct) && ct < s.best_t) { s.best_t = ct; s.best = ti; }
     }
+}
+
+__device__ __forceinline__ bool trav_pop(Trav& s, const uint2* sstack, uint32_t sstride, const uint2* lstack) {
     if ((s.ng.y & 0xFF000000u) == 0u) {
         if (s.sp == 0) return false;
         --s.sp;
         s.ng = (s.sp < VMN_SH_STACK) ? sstack[s.sp * sstride] : lstack[s.sp - VMN_SH_STACK];
     }
     return true;
+}
+
+// Warp-pooled triangle tests. After a node visit only ~3 of 32 lanes have triangles pending, and a per-lane loop makes
+// the whole warp wait for the lane with the most (the first ncu source view: 43 % of k_extend's issue slots at 3.3 active
+// threads). Here the warp's pending (ray, triangle) pairs are numbered by a prefix sum and dealt one per lane: lane j takes
+// pair j, fetches the owner's ray by shuffle, tests, and posts t to shared memory; each owner then folds its results in
+// triangle order with the reference's strict `<` (bvh.cpp:90), so the outcome is identical to the per-lane loop.
+// wscratch: 64 words of shared memory per warp. Must be called by all 32 lanes.
+template <bool COUNT>
+__device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const SceneDev& sc, uint32_t* wscratch, TravCounters* cnt) {
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t bits = active ? s.tg.y : 0u;
+    const uint32_t n = __popc(bits);
+    const uint32_t total = __reduce_add_sync(FULL, n);
+    if (total == 0u) return;
+    uint32_t incl = n;
+#pragma unroll
+    for (int dlt = 1; dlt < 32; dlt <<= 1) {
+        const uint32_t up = __shfl_up_sync(FULL, incl, dlt);
+        if ((int)lane >= dlt) incl += up;
+    }
+    const uint32_t excl = incl - n;
+    uint32_t* w_owner = wscratch;
+    float* w_res = reinterpret_cast<float*>(wscratch + 32);
+    for (uint32_t w0 = 0; w0 < total; w0 += 32u) { // warp-uniform; one trip unless more than 32 pairs are pending
+        const bool has = n != 0u && excl < w0 + 32u && incl > w0;
+        const uint32_t lo = excl > w0 ? excl : w0;          // first of my pairs inside the window
+        const uint32_t p0 = lo - w0;
+        if (has) w_owner[p0] = lane;
+        const uint32_t heads = __reduce_or_sync(FULL, has ? (1u << p0) : 0u);
+        __syncwarp();
+        const uint32_t j = w0 + lane;
+        const bool work = j < total;
+        uint32_t owner = lane;
+        if (work) owner = w_owner[31u - __clz(heads & (0xFFFFFFFFu >> (31u - lane)))];
+        const uint32_t o_excl = __shfl_sync(FULL, excl, owner), o_bits = __shfl_sync(FULL, bits, owner), o_base = __shfl_sync(FULL, s.tg.x, owner);
+        const float ox = __shfl_sync(FULL, s.o.x, owner), oy = __shfl_sync(FULL, s.o.y, owner), oz = __shfl_sync(FULL, s.o.z, owner);
+        const float dx = __shfl_sync(FULL, s.d.x, owner), dy = __shfl_sync(FULL, s.d.y, owner), dz = __shfl_sync(FULL, s.d.z, owner);
+        if (work) {
+            uint32_t b = o_bits;
+            for (uint32_t k = j - o_excl; k; --k) b &= b - 1u;
+            const TriRec T = load_tri(sc.tris + o_base + (__ffs(b) - 1u));
+            if (COUNT) ++cnt->tris;
+            float ct;
+            w_res[lane] = tri_intersect(T, V3(ox, oy, oz), V3(dx, dy, dz), &ct) ? ct : INFINITY;
+        }
+        __syncwarp();
+        if (has) {
+            uint32_t b = bits;
+            for (uint32_t k = lo - excl; k; --k) b &= b - 1u;
+            const uint32_t hi = incl < w0 + 32u ? incl : w0 + 32u;
+            for (uint32_t q = p0; q < p0 + (hi - lo); ++q) {
+                const float ct = w_res[q];
+                const uint32_t ti = s.tg.x + (__ffs(b) - 1u);
+                b &= b - 1u;
+                if (ct < s.best_t) { s.best_t = ct; s.best = ti; }
+            }
+        }
+        __syncwarp();
+    }
+    s.tg.y = 0u;
 }
 
 // single-ray form: returns the index into sc.tris of the closest triangle (or VMN_MISS) and its t
@@ -172,7 +258,10 @@ __device__ __forceinline__ uint32_t trace_wide(const SceneDev& sc, V3 o, V3 d, f
     Trav s;
     uint2 lstack[VMN_LOCAL_STACK];
     if (trav_init(s, sc, o, d))
-        while (trav_step<COUNT>(s, sc, sstack, sstride, lstack, cnt)) {}
+        do {
+            trav_node<COUNT>(s, sc, sstack, sstride, lstack, cnt);
+            trav_tris<COUNT>(s, sc, cnt);
+        } while (trav_pop(s, sstack, sstride, lstack));
     *t_out = s.best_t;
     return s.best;
 }
@@ -182,13 +271,15 @@ __device__ __forceinline__ uint32_t trace_wide(const SceneDev& sc, V3 o, V3 d, f
 // counter (one atomicAdd per chunk, by one lane, broadcast with a shuffle) and hands them to idle lanes by ballot/popc
 // rank, as soon as at least `refill_min` lanes are idle. The first profile of the one-batch-per-warp version showed
 // 3.4 of 32 threads active per instruction: a few long rays kept a warp alive while the other lanes sat finished.
-// load(i, &o, &d) reads ray i; store(i, trav) writes its result.
+// load(i, &o, &d) reads ray i; store(i, trav) writes its result. wscratch: 64 words of shared memory per warp.
 template <bool COUNT, class LoadRay, class StoreHit>
 __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n, unsigned long long* next, uint32_t chunk, uint32_t refill_min,
-                                                 uint2* sstack, uint32_t sstride, TravCounters* cnt, LoadRay load, StoreHit store) {
+                                                 uint2* sstack, uint32_t sstride, uint32_t* wscratch, TravCounters* cnt, LoadRay load,
+                                                 StoreHit store) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t FULL = 0xffffffffu;
     Trav s;
+    s.tg = make_uint2(0u, 0u);
     uint2 lstack[VMN_LOCAL_STACK];
     bool active = false, exhausted = false;
     uint64_t ray = 0, wbase = 0;
@@ -220,7 +311,14 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
             if (exhausted) break;
             continue;
         }
-        if (active && !trav_step<COUNT>(s, sc, sstack, sstride, lstack, cnt)) {
+        if (active) trav_node<COUNT>(s, sc, sstack, sstride, lstack, cnt);
+#if VMN_COOP
+        __syncwarp();
+        trav_tris_coop<COUNT>(s, active, sc, wscratch, cnt);
+#else
+        if (active) trav_tris<COUNT>(s, sc, cnt);
+#endif
+        if (active && !trav_pop(s, sstack, sstride, lstack)) {
             store(ray, s);
             active = false;
         }
@@ -340,15 +438,28 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
         r.uv1 = s1.w * w0 + s3.x * w1 + s3.z * w2; // uv0.y, uv1.y, uv2.y
         r.N = normalize(-n);                        // triangle.cpp:86, meshEngine.cpp:369
     }
-    for (uint32_t i = 0; i < sc.n_spheres; ++i) { // meshEngine.cpp:377-500, fixed order, 0 < ts < nearest
-        const SphereDev s = sph[i];
-        float th = sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r);
+    // meshEngine.cpp:377-500: fixed order, accept 0 < ts < nearest. The solves do not depend on each other, only the accept
+    // chain does: for the reference's eight spheres they are issued together so that the eight fp64 sqrt chains overlap.
+    auto accept = [&](const SphereDev& s, float th) {
         if (th > 0.f && th < nearest) {
             nearest = th;
             if (s.ex != 0.f || s.ey != 0.f || s.ez != 0.f) r.Le = V3(s.ex, s.ey, s.ez);
             V3 nn = normalize(o + (d * nearest) - V3(s.nx, s.ny, s.nz));
             r.N = (s.flags & VMN_SPH_FLIP_NORMAL) ? -nn : nn;
         }
+    };
+#if VMN_SPH_UNROLL
+    if (sc.n_spheres == 8u) {
+        float th[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) th[i] = sphere_intersect(o, d, V3(sph[i].cx, sph[i].cy, sph[i].cz), sph[i].r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) accept(sph[i], th[i]);
+    } else
+#endif
+    for (uint32_t i = 0; i < sc.n_spheres; ++i) {
+        const SphereDev s = sph[i];
+        accept(s, sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r));
     }
     r.P = o + (d * nearest);
     r.dist = nearest;

@@ -160,16 +160,20 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
 }
 
 // ---- extend ----------------------------------------------------------------------------------------
+#ifndef VMN_EXTEND_MINB
+#define VMN_EXTEND_MINB 8
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(kWfBlock) k_extend(SceneDev sc, const float4* __restrict__ rays, const uint32_t* __restrict__ qcount,
+__global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev sc, const float4* __restrict__ rays, const uint32_t* __restrict__ qcount,
                                                      float2* __restrict__ hits, unsigned long long* next, TravCounters* gcnt,
                                                      unsigned long long* total_rays, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
+    __shared__ uint32_t wscratch_all[64 * (kWfBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     const uint64_t n = *qcount;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total_rays, (unsigned long long)n);
     TravCounters cnt{0ull, 0ull};
-    persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, &cnt,
+    persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) {
                                 const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
                                 *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
@@ -208,7 +212,10 @@ __device__ __forceinline__ V3 diffuse_dir(V3 N, V3 rDir, float c1, float s1, flo
 }
 
 // One iteration of Radiance()'s loop (pathtracer.cpp:36-196) for every queued ray.
-__global__ void __launch_bounds__(kWfBlock) k_shade(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, RoundParams rp,
+#ifndef VMN_SHADE_MINB
+#define VMN_SHADE_MINB 8
+#endif
+__global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, RoundParams rp,
                                                     const float4* __restrict__ rays, const float2* __restrict__ hits,
                                                     const uint32_t* __restrict__ qcount_in, float4* __restrict__ rays_out,
                                                     uint32_t* __restrict__ qcount_out, float4* __restrict__ radiance, float4* __restrict__ thr,
@@ -264,14 +271,18 @@ __global__ void __launch_bounds__(kWfBlock) k_shade(SceneDev sc, const SphereDev
                         float r1 = (float)(2 * 3.14159265358979323846 * rng.next01());
                         float r2 = (float)((double)r2scale * rng.next01());
                         float r2s = sqrtf(r2);
-                        nDir = diffuse_dir(h.N, rDir, (float)cos((double)r1), (float)sin((double)r1), r2s, sqrtf(1 - r2));
+                        double s1, c1;
+                        sincos((double)r1, &s1, &c1); // cos(r1), sin(r1) of pathtracer.cpp:160 (float r1 promoted to double)
+                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, sqrtf(1 - r2));
                         nStart = h.P - rDir * 0.001f;
                     } else { // sphere-only hit :166-190
                         double r1 = 2 * 3.14159265358979323846 * rng.next01();
                         double r2 = (double)r2scale * rng.next01();
                         float r2s = (float)sqrt(r2);
                         rng.next01(); rng.next01(); rng.next01();
-                        nDir = diffuse_dir(h.N, rDir, (float)cos(r1), (float)sin(r1), r2s, (float)sqrt(1 - r2));
+                        double s1, c1;
+                        sincos(r1, &s1, &c1);
+                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, (float)sqrt(1 - r2));
                         nStart = h.P - rDir * 0.001f;
                     }
                 }

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvermilion_b200.so")
+LIB_PATH = os.environ.get("VMN_LIB") or os.path.join(_HERE, "libvermilion_b200.so")  # VMN_LIB: experiment variants (csrc/Makefile)
 
 RAY = np.dtype([("o", "<f4", 3), ("pad0", "<f4"), ("d", "<f4", 3), ("pad1", "<f4")])
 HIT = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("tri", "<u4")])
