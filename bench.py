@@ -248,6 +248,7 @@ def main():
 
     # ---- e2e: host buffers through the C ABI, every step: scene upload + BVH build + render + image read-back ----
     ppos = torch.from_numpy(pos).pin_memory().numpy(); pnrm = torch.from_numpy(nrm).pin_memory().numpy(); puv = torch.from_numpy(uv).pin_memory().numpy()
+    pimg = torch.empty((npix, 5), dtype=torch.float32).pin_memory().numpy()  # the caller's (pinned) image buffer, like Camera::mImage
     e2e_steps = max(1, min(args.steps, 3))
     barrier()
     t0 = time.perf_counter()
@@ -258,9 +259,9 @@ def main():
         eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
         if world > 1:
             vd.reduce_film(film_t)
-            img = eng.resolve_device(d_film)
+            img = eng.resolve_device(d_film, out=pimg)
         else:
-            img = eng.read_image()
+            img = eng.read_image(out=pimg)
         e2e_rays += eng.stats()["rays_traced"]
     barrier()
     e2e_s = time.perf_counter() - t0

@@ -112,6 +112,8 @@ def main():
         ref = orc.intersect(rays[:n].view(checker.RAY).reshape(-1))
         c = common.classify_hits(h8[:n], ref)
         out["oracle_check"] = dict(c, seconds=time.time() - t0)
+        rn, rt = orc.intersect_stats(rays[:n].view(checker.RAY).reshape(-1))
+        out["reference_tree_visits"] = {"nodes_per_ray": rn / n, "tris_per_ray": rt / n, "note": "binary midpoint-split BVH of bvh.cpp:179-279, 48-byte nodes"}
         t0 = time.time()
         a, b = orc.intersect(rays[:n].view(checker.RAY).reshape(-1)), None
         cpu_s = time.time() - t0

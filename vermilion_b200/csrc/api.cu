@@ -108,6 +108,7 @@ void vmn_destroy(vmn_ctx* c) {
     for (DevBuf* b : {&c->pos, &c->nrm, &c->uv, &c->tris, &c->tris_sorted, &c->tris_orig, &c->shade, &c->wide, &c->b_min, &c->b_max,
                       &c->b_child, &c->spheres, &c->tex, &c->film, &c->q_in, &c->q_out, &c->counters})
         dev_free(*b);
+    for (DevBuf& b : c->build_scratch) dev_free(b);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -134,7 +135,7 @@ vmn_status vmn_synchronize(vmn_ctx* c) {
 }
 
 static vmn_status upload(vmn_ctx* c, DevBuf& b, const void* src, size_t bytes) {
-    vmn_status s = dev_alloc(c, b, bytes);
+    vmn_status s = dev_reserve(c, b, bytes); // grow-only: re-uploading a same-sized scene does not reallocate
     if (s != VMN_OK) return s;
     if (bytes) VMN_CUDA(c, cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
     return VMN_OK;
@@ -148,8 +149,9 @@ vmn_status vmn_scene_set_triangles(vmn_ctx* c, const float* pos, const float* nr
     c->n_tris = 0;
     vmn_status s;
     if ((s = upload(c, c->pos, pos, 36ull * n)) != VMN_OK) return s;
-    if (nrm) { if ((s = upload(c, c->nrm, nrm, 36ull * n)) != VMN_OK) return s; } else dev_free(c->nrm);
-    if (uv) { if ((s = upload(c, c->uv, uv, 24ull * n)) != VMN_OK) return s; } else dev_free(c->uv);
+    c->have_nrm = nrm != nullptr; c->have_uv = uv != nullptr;
+    if (nrm && (s = upload(c, c->nrm, nrm, 36ull * n)) != VMN_OK) return s;
+    if (uv && (s = upload(c, c->uv, uv, 24ull * n)) != VMN_OK) return s;
     VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // host pointers are borrowed for the call only
     c->n_tris = n;
     return VMN_OK;
@@ -209,8 +211,7 @@ vmn_status vmn_scene_commit(vmn_ctx* c) {
     if (s != VMN_OK) return s;
     c->scene.n_spheres = c->n_spheres;
     c->scene.tex = c->tex.as<float>(); c->scene.tex_w = c->tex_w; c->scene.tex_h = c->tex_h; c->scene.tex_c = c->tex_c;
-    // the staged host arrays are no longer needed
-    dev_free(c->pos); dev_free(c->nrm); dev_free(c->uv);
+    // the staged arrays stay allocated (reused by the next vmn_scene_set_triangles); they are 96 B/triangle
     c->committed = true;
     return VMN_OK;
 }

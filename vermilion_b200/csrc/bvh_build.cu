@@ -203,7 +203,7 @@ __device__ __forceinline__ float box_area(float4 a, float4 b) {
 __global__ void k_collapse(const uint2* __restrict__ q_in, uint32_t n_in, uint2* __restrict__ q_out, CollapseCtl* ctl, int n,
                            const int2* __restrict__ child, const int* __restrict__ first, const uint32_t* __restrict__ count,
                            const float4* __restrict__ bmin, const float4* __restrict__ bmax, const TriRec* __restrict__ tris_sorted,
-                           WideNode* __restrict__ nodes, TriRec* __restrict__ tris) {
+                           WideNode* __restrict__ nodes, LeafTri* __restrict__ tris) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_in) return;
     const int bnode = (int)q_in[w].x;
@@ -305,12 +305,12 @@ __global__ void k_collapse(const uint2* __restrict__ q_in, uint32_t n_in, uint2*
             uint32_t cnt = count[c];
             uint32_t f = (c < nint) ? (uint32_t)first[c] : (uint32_t)(c - nint);
             meta[s] = (uint8_t)((((1u << cnt) - 1u) << 5) | toff);
-            for (uint32_t j = 0; j < cnt; ++j) tris[tbase + toff + j] = tris_sorted[f + j];
+            for (uint32_t j = 0; j < cnt; ++j) { const TriRec t = tris_sorted[f + j]; LeafTri& o = tris[tbase + toff + j]; o.r0 = t.r0; o.r1 = t.r1; o.r2 = t.r2; }
             toff += cnt;
         }
     }
     auto pack4 = [](const uint8_t* b) { return (uint32_t)b[0] | ((uint32_t)b[1] << 8) | ((uint32_t)b[2] << 16) | ((uint32_t)b[3] << 24); };
-    WideNode nd;
+    WideNode nd{};
     nd.q0 = make_uint4(__float_as_uint(pl[0]), __float_as_uint(pl[1]), __float_as_uint(pl[2]), eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24));
     nd.q1 = make_uint4(cbase, tbase, pack4(meta), pack4(meta + 4));
     nd.q2 = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
@@ -330,17 +330,21 @@ vmn_status build_bvh(vmn_ctx* c) {
     c->scene.n_tris = n;
     c->n_wide = 0;
     c->stats.n_triangles = n; c->stats.n_nodes = 0; c->stats.n_wide_nodes = 0;
-    c->stats.node_bytes = sizeof(WideNode); c->stats.tri_bytes = sizeof(TriRec);
+    c->stats.node_bytes = 80; c->stats.tri_bytes = 48; // payload bytes
     if (n == 0) return VMN_OK;
 
     VMN_CUDA(c, cudaEventRecord(c->ev[0], st));
     const uint32_t nnodes = 2 * n - 1;
-    DevBuf pmin, pmax, keys, keys2, vals, vals2, parent, first, count, flags, sb, tmp, qa, qb, ctl;
+    // build scratch lives in the context and only grows: a re-commit of a same-sized scene (per-frame rebuild, bench e2e) does not
+    // touch cudaMalloc/cudaFree (cudaFree synchronises the device; 15 of them per build cost more than the build itself)
+    DevBuf &pmin = c->build_scratch[0], &pmax = c->build_scratch[1], &keys = c->build_scratch[2], &keys2 = c->build_scratch[3],
+           &vals = c->build_scratch[4], &vals2 = c->build_scratch[5], &parent = c->build_scratch[6], &first = c->build_scratch[7],
+           &count = c->build_scratch[8], &flags = c->build_scratch[9], &sb = c->build_scratch[10], &tmp = c->build_scratch[11],
+           &qa = c->build_scratch[12], &qb = c->build_scratch[13], &ctl = c->build_scratch[14];
     vmn_status s = VMN_OK;
-    auto cleanup = [&]() {
-        for (DevBuf* b : {&pmin, &pmax, &keys, &keys2, &vals, &vals2, &parent, &first, &count, &flags, &sb, &tmp, &qa, &qb, &ctl}) dev_free(*b);
-    };
+    auto cleanup = [&]() {};
 #define TRY(x) do { s = (x); if (s != VMN_OK) { cleanup(); return s; } } while (0)
+#define dev_alloc dev_reserve /* grow-only inside the build */
 #define TRYCUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) { cleanup(); return fail(c, VMN_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e__)); } } while (0)
     TRY(dev_alloc(c, pmin, 16ull * n)); TRY(dev_alloc(c, pmax, 16ull * n));
     TRY(dev_alloc(c, keys, 8ull * n)); TRY(dev_alloc(c, keys2, 8ull * n));
@@ -351,7 +355,7 @@ vmn_status build_bvh(vmn_ctx* c) {
     TRY(dev_alloc(c, c->b_min, 16ull * nnodes)); TRY(dev_alloc(c, c->b_max, 16ull * nnodes));
     TRY(dev_alloc(c, c->b_child, 8ull * n));
     TRY(dev_alloc(c, c->tris_sorted, sizeof(TriRec) * (uint64_t)n));
-    TRY(dev_alloc(c, c->tris, sizeof(TriRec) * (uint64_t)n));
+    TRY(dev_alloc(c, c->tris, sizeof(LeafTri) * (uint64_t)n));
     TRY(dev_alloc(c, c->tris_orig, sizeof(TriRec) * (uint64_t)n));
     TRY(dev_alloc(c, c->shade, sizeof(ShadeRec) * (uint64_t)n));
     TRY(dev_alloc(c, c->wide, sizeof(WideNode) * (uint64_t)n));
@@ -369,7 +373,7 @@ vmn_status build_bvh(vmn_ctx* c) {
                                             vals2.as<uint32_t>(), (int)n, 0, 63, st));
     k_leaves<<<cdiv(n, B), B, 0, st>>>(pos, vals2.as<uint32_t>(), n, pmin.as<float4>(), pmax.as<float4>(), c->b_min.as<float4>(),
                                        c->b_max.as<float4>(), c->tris_sorted.as<TriRec>(), count.as<uint32_t>());
-    k_orig_records<<<cdiv(n, B), B, 0, st>>>(pos, c->nrm.as<float>(), c->uv.as<float>(), n, c->tris_orig.as<TriRec>(), c->shade.as<ShadeRec>());
+    k_orig_records<<<cdiv(n, B), B, 0, st>>>(pos, c->have_nrm ? c->nrm.as<float>() : nullptr, c->have_uv ? c->uv.as<float>() : nullptr, n, c->tris_orig.as<TriRec>(), c->shade.as<ShadeRec>());
     TRYCUDA(cudaMemsetAsync(flags.p, 0, 4ull * n, st));
     if (n > 1) {
         k_hierarchy<<<cdiv(n - 1, B), B, 0, st>>>(keys2.as<uint64_t>(), (int)n, c->b_child.as<int2>(), parent.as<int>(), first.as<int>());
@@ -389,7 +393,7 @@ vmn_status build_bvh(vmn_ctx* c) {
     while (n_in) {
         k_collapse<<<cdiv(n_in, 128), 128, 0, st>>>(qi->as<uint2>(), n_in, qo->as<uint2>(), ctl.as<CollapseCtl>(), (int)n, c->b_child.as<int2>(),
                                                     first.as<int>(), count.as<uint32_t>(), c->b_min.as<float4>(), c->b_max.as<float4>(),
-                                                    c->tris_sorted.as<TriRec>(), c->wide.as<WideNode>(), c->tris.as<TriRec>());
+                                                    c->tris_sorted.as<TriRec>(), c->wide.as<WideNode>(), c->tris.as<LeafTri>());
         TRYCUDA(cudaMemcpyAsync(&h, ctl.p, sizeof(h), cudaMemcpyDeviceToHost, st));
         TRYCUDA(cudaStreamSynchronize(st));
         n_in = h.q_out;
@@ -405,10 +409,11 @@ vmn_status build_bvh(vmn_ctx* c) {
     cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
     cleanup();
 #undef TRY
+#undef dev_alloc
 #undef TRYCUDA
 
     c->scene.nodes = c->wide.as<WideNode>();
-    c->scene.tris = c->tris.as<TriRec>();
+    c->scene.tris = c->tris.as<LeafTri>();
     c->scene.tris_sorted = c->tris_sorted.as<TriRec>();
     c->scene.tris_orig = c->tris_orig.as<TriRec>();
     c->scene.shade = c->shade.as<ShadeRec>();

@@ -53,8 +53,29 @@ struct ShadeRec { float4 s0, s1, s2, s3; };
 //   q4 = (qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7])
 // child box = p + q * 2^(e-127) per axis. meta[i]: 0 = empty; internal = (1<<5) | (24+i);
 // leaf = (unary triangle count 1|3|7) << 5 | offset of its first triangle from tri_base (0..23).
-struct WideNode { uint4 q0, q1, q2, q3, q4; };
-static_assert(sizeof(WideNode) == 80, "WideNode must be 80 bytes");
+// VMN_NODE_PAD / VMN_TRI_PAD (in 16-byte units) pad the records of the two traversal arrays to a sector-friendly stride
+// (experiment knobs; the algorithmic byte counts of the roofline always use the 80 / 48 payload bytes).
+#ifndef VMN_NODE_PAD
+#define VMN_NODE_PAD 0
+#endif
+#ifndef VMN_TRI_PAD
+#define VMN_TRI_PAD 1 // 64-byte leaf triangles = exactly two 32-byte sectors: +3.7 % on C3, +1 % on C2
+#endif
+struct WideNode {
+    uint4 q0, q1, q2, q3, q4;
+#if VMN_NODE_PAD
+    uint4 pad[VMN_NODE_PAD];
+#endif
+};
+// triangle record of the BVH8 leaf-order array (same payload as TriRec)
+struct LeafTri {
+    float4 r0, r1, r2;
+#if VMN_TRI_PAD
+    float4 pad[VMN_TRI_PAD];
+#endif
+};
+constexpr uint32_t kNodeStride16 = sizeof(WideNode) / 16, kLeafTriStride16 = sizeof(LeafTri) / 16;
+static_assert(sizeof(WideNode) == 80 + 16 * VMN_NODE_PAD, "WideNode payload must be 80 bytes");
 static_assert(sizeof(TriRec) == 48, "TriRec must be 48 bytes");
 
 // Binary LBVH (build intermediate and the BVH2 baseline traversal). Node i < n-1 internal,
@@ -68,7 +89,7 @@ struct Bvh2 {
 
 struct SceneDev {
     const WideNode* nodes;   // BVH8
-    const TriRec* tris;      // in BVH8 leaf order
+    const LeafTri* tris;     // in BVH8 leaf order
     const TriRec* tris_sorted; // in Morton order (BVH2 leaves)
     const ShadeRec* shade;   // by original id
     const TriRec* tris_orig; // by original id (for barycentrics / getNormal)

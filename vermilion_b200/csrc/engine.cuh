@@ -32,11 +32,13 @@ struct vmn_ctx {
     // host-provided scene, staged on the device until commit
     vmn::DevBuf pos, nrm, uv;
     uint64_t n_tris = 0;
+    bool have_nrm = false, have_uv = false;
     bool committed = false;
 
     // built scene
     vmn::DevBuf tris, tris_sorted, tris_orig, shade, wide, b_min, b_max, b_child;
     vmn::DevBuf spheres, tex;
+    vmn::DevBuf build_scratch[15]; // bvh_build.cu, grow-only
     uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0;
     uint64_t n_wide = 0;
     vmn::SceneDev scene{};

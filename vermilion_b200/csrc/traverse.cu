@@ -29,17 +29,6 @@ __device__ __forceinline__ void load_ray(const vmn_ray* __restrict__ rays, uint6
     *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
 }
 
-// closest hit; returns original triangle id (or VMN_MISS) and t
-template <bool WIDE, bool COUNT>
-__device__ __forceinline__ uint32_t closest_hit(const SceneDev& sc, V3 o, V3 d, float* t, uint2* sstack, TravCounters* cnt) {
-    uint32_t k;
-    const TriRec* base;
-    if (WIDE) { k = trace_wide<COUNT>(sc, o, d, t, sstack, kTraceBlock, cnt); base = sc.tris; }
-    else { k = trace_bvh2<COUNT>(sc, o, d, t, cnt); base = sc.tris_sorted; }
-    if (k == VMN_MISS) return VMN_MISS;
-    return __float_as_uint(__ldg(&reinterpret_cast<const float4*>(base + k)->w));
-}
-
 template <bool WIDE, bool COUNT>
 __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
                                                            vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt,
@@ -48,11 +37,9 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
     __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
-    auto finish = [&](uint64_t i, V3 o, V3 d, float t, uint32_t k, const TriRec* base) {
-        uint32_t id = VMN_MISS;
+    auto finish = [&](uint64_t i, V3 o, V3 d, float t, uint32_t id) { // id: original triangle id or VMN_MISS
         float u = 0.f, v = 0.f;
-        if (k != VMN_MISS) {
-            id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(base + k)->w));
+        if (id != VMN_MISS) {
             const V3 hp = o + d * t; // bvh.cpp:140
             tri_bary(load_tri(sc.tris_orig + id), hp, &u, &v);
         }
@@ -61,7 +48,7 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
     if (WIDE) {
         persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
                                 [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
-                                [&](uint64_t i, const Trav& s) { finish(i, s.o, s.d, s.best_t, s.best, sc.tris); });
+                                [&](uint64_t i, const Trav& s) { finish(i, s.o, s.d, s.best_t, leaf_original_id(sc.tris, s.best)); });
     } else {
         uint64_t i;
         while (claim_rays(next, n, &i)) {
@@ -70,17 +57,13 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
             load_ray(rays, i, &o, &d);
             float t;
             const uint32_t k = trace_bvh2<COUNT>(sc, o, d, &t, &cnt);
-            finish(i, o, d, t, k, sc.tris_sorted);
+            finish(i, o, d, t, k == VMN_MISS ? VMN_MISS : __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris_sorted + k)->w)));
         }
     }
     if (COUNT) {
         atomicAdd(&gcnt->nodes, cnt.nodes);
         atomicAdd(&gcnt->tris, cnt.tris);
     }
-}
-
-__device__ __forceinline__ uint32_t original_id(const SceneDev& sc, uint32_t k) {
-    return k == VMN_MISS ? VMN_MISS : __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + k)->w));
 }
 
 __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_occluded(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n, uint8_t* __restrict__ out,
@@ -103,7 +86,7 @@ __global__ void __launch_bounds__(kTraceBlock, 6) k_raycast(SceneDev sc, const S
     persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
                             [&](uint64_t i, const Trav& s) {
-                                const RayCastOut r = raycast_finish(sc, sph, s.o, s.d, s.best_t, original_id(sc, s.best));
+                                const RayCastOut r = raycast_finish(sc, sph, s.o, s.d, s.best_t, leaf_original_id(sc.tris, s.best));
                                 float4* q = reinterpret_cast<float4*>(out + i);
                                 q[0] = make_float4(r.P.x, r.P.y, r.P.z, r.dist);
                                 q[1] = make_float4(r.N.x, r.N.y, r.N.z, __uint_as_float((r.hit ? VMN_RC_HIT : 0u) | (r.material ? VMN_RC_MATERIAL : 0u)));

@@ -21,6 +21,9 @@ namespace vmn {
 #ifndef VMN_SPH_UNROLL
 #define VMN_SPH_UNROLL 0
 #endif
+#ifndef VMN_PREFETCH
+#define VMN_PREFETCH 0
+#endif
 #ifndef VMN_COOP
 #define VMN_COOP 1            // warp-pooled triangle tests (trav_tris_coop); 0 = per-lane loop
 #endif
@@ -50,6 +53,15 @@ __device__ __forceinline__ TriRec load_tri(const TriRec* __restrict__ p) {
     const float4* q = reinterpret_cast<const float4*>(p);
     TriRec t; t.r0 = __ldg(q); t.r1 = __ldg(q + 1); t.r2 = __ldg(q + 2);
     return t;
+}
+__device__ __forceinline__ TriRec load_tri(const LeafTri* __restrict__ p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+    TriRec t; t.r0 = __ldg(q); t.r1 = __ldg(q + 1); t.r2 = __ldg(q + 2);
+    return t;
+}
+// original triangle id of leaf-order record k (or VMN_MISS)
+__device__ __forceinline__ uint32_t leaf_original_id(const LeafTri* __restrict__ tris, uint32_t k) {
+    return k == VMN_MISS ? VMN_MISS : __float_as_uint(__ldg(&reinterpret_cast<const float4*>(tris + k)->w));
 }
 
 __device__ __forceinline__ bool ray_is_nan(V3 o, V3 d) {
@@ -134,7 +146,7 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             if (s.sp < VMN_SH_STACK) sstack[s.sp * sstride] = s.ng; else lstack[s.sp - VMN_SH_STACK] = s.ng;
             ++s.sp;
         }
-        const uint4* np = nodes + 5ull * nidx;
+        const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
         const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
         if (COUNT) ++cnt->nodes;
         // per-axis: t(q) = q * a + b with a = 2^(e-127) / d, b = (p - o) / d, evaluated as fma(1 + q*2^-15, A, B), A = a * 2^15,
@@ -160,6 +172,18 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
 #undef VMN_CH
         s.ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
         s.tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
+#if VMN_PREFETCH
+        // the nearest internal child hit is the next node this ray visits (unless a triangle test culls it): start pulling it into L2
+        // now, so that its DRAM latency overlaps the triangle phase instead of following it
+        if (s.ng.y & 0xFF000000u) {
+            const uint32_t nslot = ((31u - __clz(s.ng.y)) - 24u) ^ s.oct_inv;
+            const uint4* nx = nodes + (uint64_t)kNodeStride16 * (s.ng.x + __popc(s.ng.y & 0xFFu & ((1u << nslot) - 1u)));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nx));
+#if VMN_PREFETCH > 1
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 4));
+#endif
+        }
+#endif
     } else {
         s.tg = s.ng;
         s.ng = make_uint2(0u, 0u);

@@ -179,9 +179,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev s
                                 *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
                             },
                             [&](uint64_t i, const Trav& s) {
-                                uint32_t id = VMN_MISS;
-                                if (s.best != VMN_MISS) id = __float_as_uint(__ldg(&reinterpret_cast<const float4*>(sc.tris + s.best)->w));
-                                hits[i] = make_float2(s.best_t, __uint_as_float(id));
+                                hits[i] = make_float2(s.best_t, __uint_as_float(leaf_original_id(sc.tris, s.best)));
                             });
     if (COUNT) { atomicAdd(&gcnt->nodes, cnt.nodes); atomicAdd(&gcnt->tris, cnt.tris); }
 }

@@ -226,9 +226,13 @@ class Engine:
         prm = RenderParams(mode, max_segments, seed, pixel_begin, pixel_end, sample_begin, sample_end, tile_size, tile_rank, tile_world, 0)
         self._chk(self.L.vmn_render(self.h, C.byref(prm)), "vmn_render")
 
-    def read_image(self, layout=FILM_RGBAZ):
+    def read_image(self, layout=FILM_RGBAZ, out=None):
+        """out: optional preallocated float32 array (e.g. pinned host memory) of shape [pixels, 5 | 4]."""
         npx = self.cam.width * self.cam.height
-        out = np.empty((npx, 5 if layout == FILM_RGBAZ else 4), np.float32)
+        shape = (npx, 5 if layout == FILM_RGBAZ else 4)
+        if out is None:
+            out = np.empty(shape, np.float32)
+        assert out.dtype == np.float32 and out.shape == shape and out.flags.c_contiguous
         self._chk(self.L.vmn_read_image(self.h, _p(out), layout), "vmn_read_image")
         return out
 
@@ -237,9 +241,11 @@ class Engine:
         self._chk(self.L.vmn_film_device(self.h, C.byref(ptr), C.byref(n)), "vmn_film_device")
         return ptr.value, n.value
 
-    def resolve_device(self, d_sum_ptr):
+    def resolve_device(self, d_sum_ptr, out=None):
         npx = self.cam.width * self.cam.height
-        out = np.empty((npx, 5), np.float32)
+        if out is None:
+            out = np.empty((npx, 5), np.float32)
+        assert out.dtype == np.float32 and out.shape == (npx, 5) and out.flags.c_contiguous
         self._chk(self.L.vmn_film_resolve_device(self.h, d_sum_ptr, _p(out)), "vmn_film_resolve_device")
         return out
 
