@@ -15,6 +15,10 @@ import argparse
 import ctypes
 import json
 import os
+
+# torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU reference arm must use all host cores (libgomp reads this when it loads)
+if os.environ.get("OMP_NUM_THREADS") == "1" and "--impl" in " ".join(os.sys.argv):
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
 import subprocess
 import sys
 import tempfile

@@ -111,8 +111,9 @@ typedef struct {
     uint32_t sample_begin, sample_end; /* FIXED: sample slice [begin,end) of the spp-long sequence; end = 0 -> spp */
     uint32_t tile_size;     /* 0 = contiguous pixel range; else pixel_begin/end index interleaved tiles (see vmn_render) */
     uint32_t tile_rank, tile_world; /* tile t belongs to this context iff t % tile_world == tile_rank */
-    uint32_t reserved;
+    uint32_t flags;         /* VMN_RENDER_* */
 } vmn_render_params;
+#define VMN_RENDER_ACCUMULATE 1u /* keep the film and add to it (progressive rendering: successive sample slices, FIXED mode) */
 
 typedef struct {
     uint64_t n_triangles, n_nodes, n_wide_nodes;

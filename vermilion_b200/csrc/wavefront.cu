@@ -535,7 +535,8 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     }
     c->stats.kernel_launches = 0; c->stats.rays_traced = 0; c->stats.paths_traced = 0;
     c->stats.raygen_ms = c->stats.extend_ms = c->stats.shade_ms = c->stats.resolve_ms = c->stats.total_ms = 0;
-    VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
+    if ((prm->flags & VMN_RENDER_ACCUMULATE) && mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "VMN_RENDER_ACCUMULATE needs VMN_MODE_FIXED");
+    if (!(prm->flags & VMN_RENDER_ACCUMULATE)) VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
     if (n_local_total == 0 || s_begin == s_end) return VMN_OK;
 
     const uint64_t cap = c->max_paths;

@@ -22,6 +22,7 @@ MISS = 0xFFFFFFFF
 MODE_COMPAT, MODE_FIXED = 0, 1
 FILM_RGBAZ, FILM_SUM = 0, 1
 CFG_COUNTERS = 1
+RENDER_ACCUMULATE = 1
 ISECT_BVH2 = 1
 STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE"}
 
@@ -45,7 +46,7 @@ class Camera(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("mode", C.c_int32), ("max_segments", C.c_uint32), ("seed", C.c_uint64), ("pixel_begin", C.c_uint64),
                 ("pixel_end", C.c_uint64), ("sample_begin", C.c_uint32), ("sample_end", C.c_uint32), ("tile_size", C.c_uint32),
-                ("tile_rank", C.c_uint32), ("tile_world", C.c_uint32), ("reserved", C.c_uint32)]
+                ("tile_rank", C.c_uint32), ("tile_world", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class Stats(C.Structure):
@@ -222,8 +223,9 @@ class Engine:
         return out
 
     def render(self, mode=MODE_FIXED, seed=1, max_segments=5, pixel_begin=0, pixel_end=0, sample_begin=0, sample_end=0, tile_size=0,
-               tile_rank=0, tile_world=1):
-        prm = RenderParams(mode, max_segments, seed, pixel_begin, pixel_end, sample_begin, sample_end, tile_size, tile_rank, tile_world, 0)
+               tile_rank=0, tile_world=1, accumulate=False):
+        prm = RenderParams(mode, max_segments, seed, pixel_begin, pixel_end, sample_begin, sample_end, tile_size, tile_rank, tile_world,
+                           RENDER_ACCUMULATE if accumulate else 0)
         self._chk(self.L.vmn_render(self.h, C.byref(prm)), "vmn_render")
 
     def read_image(self, layout=FILM_RGBAZ, out=None):
