@@ -170,7 +170,7 @@ def main():
     ap.add_argument("--res", default="1920x1080")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--max-paths", type=int, default=8 << 20)
+    ap.add_argument("--max-paths", type=int, default=32 << 20, help="paths in flight (112 B each); larger batches amortise the tail of every persistent launch")
     args = ap.parse_args()
     width, height = (int(x) for x in args.res.lower().split("x"))
     if args.impl == "reference":

@@ -47,7 +47,7 @@ typedef struct vmn_ctx vmn_ctx;
 typedef struct {
     int32_t device;        /* CUDA device ordinal */
     uint32_t flags;        /* VMN_CFG_* */
-    uint64_t max_paths;    /* wavefront pool size (paths in flight); 0 = default 4 Mi */
+    uint64_t max_paths;    /* wavefront pool size (paths in flight, 112 B each); 0 = default 16 Mi */
     void* stream;          /* cudaStream_t to launch on; NULL = a stream the context creates */
 } vmn_config;
 #define VMN_CFG_COUNTERS 1u /* keep per-ray node/triangle visit counters (slower; for B_ray) */
@@ -173,6 +173,11 @@ vmn_status vmn_read_image(vmn_ctx* ctx, float* dst, int32_t layout);
 vmn_status vmn_film_device(vmn_ctx* ctx, float** d_sum, uint64_t* n_floats);
 /* resolve an (externally reduced) sum buffer already on the device into RGBAZ on the host */
 vmn_status vmn_film_resolve_device(vmn_ctx* ctx, const float* d_sum, float* dst_rgbaz);
+
+/* replaces the 32f -> 8-bit conversion loop of Camera::saveFrame (camera.cpp:138-175, RGBAZ case): rgba8[4*p+k] =
+ * (unsigned char)floor(rgbaz[5*p+k] * 255), depth[p] = rgbaz[5*p+4]. Packed on the device: 8 bytes per pixel cross PCIe instead
+ * of 20. depth may be NULL. (Writing the PNG/EXR files stays host code of the reference, camera.cpp:178-189.) */
+vmn_status vmn_read_image_rgba8(vmn_ctx* ctx, uint8_t* rgba8, float* depth);
 
 vmn_status vmn_get_stats(vmn_ctx* ctx, vmn_stats* out);
 

@@ -41,7 +41,7 @@ def child(args):
         eng.close()
     else:
         pos, nrm, uv = scenes.spheres(4, 3, 6, 150.0)
-        eng = engine.Engine(device=0, max_paths=8 << 20)
+        eng = engine.Engine(device=0, max_paths=args.max_paths)
         eng.set_scene(pos, nrm, uv)
         eng.set_camera(engine.camera_from_settings(1920, 1080, (0.0, 500.0, 1900.0), (0.0, 0.0, 0.0), 6.0, (3.6, 3.6 * 1080 / 1920), args.spp))
         best = None
@@ -63,17 +63,27 @@ def main():
     ap.add_argument("--c3", action="store_true")
     ap.add_argument("--c3-tris", type=int, default=10_000_000)
     ap.add_argument("--c3-rays", type=int, default=16_777_216)
+    ap.add_argument("--max-paths", type=int, default=8 << 20)
     ap.add_argument("--child", action="store_true")
     args = ap.parse_args()
     if args.child:
         return child(args)
     for v in args.variants:
         env = dict(os.environ)
+        # "name@K=V,K2=V2" sets environment knobs (e.g. VMN_REFILL) and/or MAXPATHS for that run
+        v, _, knobs = v.partition("@")
+        mp = args.max_paths
+        for kv in filter(None, knobs.split(",")):
+            k, _, val = kv.partition("=")
+            if k == "MAXPATHS":
+                mp = int(val)
+            else:
+                env[k] = val
         if v != "default":
             env["VMN_LIB"] = os.path.join(ROOT, "vermilion_b200", "variants", f"libvermilion_b200_{v}.so")
-        cmd = [sys.executable, os.path.abspath(__file__), "--child", "--spp", str(args.spp), "--c3-tris", str(args.c3_tris), "--c3-rays", str(args.c3_rays)] + (["--c3"] if args.c3 else [])
+        cmd = [sys.executable, os.path.abspath(__file__), "--child", "--spp", str(args.spp), "--c3-tris", str(args.c3_tris), "--c3-rays", str(args.c3_rays), "--max-paths", str(mp)] + (["--c3"] if args.c3 else [])
         r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
-        print(v, r.stdout.strip() or r.stderr[-500:], flush=True)
+        print(v, knobs, r.stdout.strip() or r.stderr[-500:], flush=True)
 
 
 if __name__ == "__main__":

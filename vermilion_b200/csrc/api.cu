@@ -84,7 +84,7 @@ vmn_status vmn_create(const vmn_config* cfg, vmn_ctx** out) {
     *out = c; // returned even on failure so that vmn_last_error can be read; caller still destroys it
     c->device = cfg ? cfg->device : 0;
     c->flags = cfg ? cfg->flags : 0;
-    c->max_paths = (cfg && cfg->max_paths) ? cfg->max_paths : (4ull << 20);
+    c->max_paths = (cfg && cfg->max_paths) ? cfg->max_paths : (16ull << 20);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
@@ -393,6 +393,23 @@ vmn_status vmn_read_image(vmn_ctx* c, float* dst, int32_t layout) {
     }
     if (layout != VMN_FILM_RGBAZ) return fail(c, VMN_ERR_INVALID, "bad layout %d", layout);
     return vmn_film_resolve_device(c, c->film.as<float>(), dst);
+}
+
+vmn_status vmn_read_image_rgba8(vmn_ctx* c, uint8_t* rgba8, float* depth) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (!rgba8) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    const uint64_t npix = c->film_pixels;
+    vmn_status s = dev_reserve(c, c->q_out, 8 * npix);
+    if (s != VMN_OK) return s;
+    uint8_t* d_rgba = c->q_out.as<uint8_t>();
+    float* d_depth = reinterpret_cast<float*>(d_rgba + 4 * npix);
+    if ((s = film_pack_rgba8(c, c->film.as<float>(), d_rgba, depth ? d_depth : nullptr, npix)) != VMN_OK) return s;
+    VMN_CUDA(c, cudaMemcpyAsync(rgba8, d_rgba, 4 * npix, cudaMemcpyDeviceToHost, c->stream));
+    if (depth) VMN_CUDA(c, cudaMemcpyAsync(depth, d_depth, 4 * npix, cudaMemcpyDeviceToHost, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VMN_OK;
 }
 
 vmn_status vmn_get_stats(vmn_ctx* c, vmn_stats* out) {

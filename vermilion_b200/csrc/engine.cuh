@@ -90,6 +90,7 @@ vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_
                               const float* d_jy, uint64_t n, vmn_ray* d_out);
 vmn_status render_frame(vmn_ctx* c, const vmn_render_params* p);
 vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix);
+vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, uint8_t* d_rgba, float* d_depth, uint64_t npix);
 void pool_destroy(vmn_ctx* c);
 void camera_matrix(const vmn_camera& cam, float m[16]);
 

@@ -18,8 +18,8 @@ namespace vmn {
 #define VMN_T_MISS 999999999.f // bvh.cpp:48
 #define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
 #define VMN_LOCAL_STACK 52     // overflow entries in local memory
-#ifndef VMN_SPH_UNROLL
-#define VMN_SPH_UNROLL 0
+#ifndef VMN_HIT8
+#define VMN_HIT8 1 // +2.7 % on k_extend (C2)
 #endif
 #ifndef VMN_PREFETCH
 #define VMN_PREFETCH 0
@@ -120,6 +120,9 @@ __device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint
     const float tfz = __fmaf_rn(byte_to_unit<J>(fzw), az, fbz);
     const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
     const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
+#if VMN_HIT8
+    return tn <= tf ? 1u : 0u; // trav_node expands the 8 hit bits once per node
+#endif
     if (tn <= tf) {
         const uint32_t m = (metaw >> (8 * J)) & 0xFFu;
         const uint32_t inner = ((m & 0x18u) == 0x18u) ? 7u : 0u;
@@ -166,10 +169,35 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
         const uint32_t ny0 = ngy ? q4.x : q2.z, ny1 = ngy ? q4.y : q2.w, fy0 = ngy ? q2.z : q4.x, fy1 = ngy ? q2.w : q4.y;
         const uint32_t nz0 = ngz ? q4.z : q3.x, nz1 = ngz ? q4.w : q3.y, fz0 = ngz ? q3.x : q4.z, fz1 = ngz ? q3.y : q4.w;
         uint32_t hitmask = 0;
+#if VMN_HIT8
+        // one hit bit per child slot, then a single expansion per node: internal hits are moved to the octant-ordered positions
+        // 24 + (slot ^ oct_inv) by three conditional bit swaps; leaf hits OR in their unary triangle masks (usually 0-2 leaves)
+        uint32_t hit8 = 0;
+#define VMN_CH(J, MW, S) hit8 |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv) << (4 * S + J)
+        VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
+        VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
+#undef VMN_CH
+        {
+            const uint32_t imask = q0.w >> 24;
+            uint32_t x = hit8 & imask;
+            if (s.oct_inv & 1u) x = ((x & 0x55u) << 1) | ((x >> 1) & 0x55u);
+            if (s.oct_inv & 2u) x = ((x & 0x33u) << 2) | ((x >> 2) & 0x33u);
+            if (s.oct_inv & 4u) x = ((x & 0x0Fu) << 4) | ((x >> 4) & 0x0Fu);
+            hitmask = x << 24;
+            uint32_t hl = hit8 & ~imask;
+            while (hl) {
+                const uint32_t j = __ffs(hl) - 1u;
+                hl &= hl - 1u;
+                const uint32_t m = __byte_perm(q1.z, q1.w, j) & 0xFFu; // byte j of the 8 meta bytes
+                hitmask |= (m >> 5) << (m & 31u);
+            }
+        }
+#else
 #define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv)
         VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
         VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
 #undef VMN_CH
+#endif
         s.ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
         s.tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
 #if VMN_PREFETCH
@@ -446,10 +474,22 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
                                                      uint32_t tri_id) {
     RayCastOut r;
     r.N = V3(0, 0, 0); r.Le = V3(0, 0, 0); r.uv0 = 0.f; r.uv1 = 0.f; r.tri = tri_id;
-    float nearest = INFINITY;
     r.material = tri_id != VMN_MISS;
+    float nearest = r.material ? bvh_t : INFINITY;
+    // meshEngine.cpp:377-500: fixed order, accept 0 < ts < nearest. The reference overwrites the normal at every accepted sphere
+    // and keeps the emission of the last accepted EMITTER, so only the last accepted sphere's normal survives: it is computed once,
+    // after the loop, with the same expression (an IEEE normalize per accept was 11 % of k_shade).
+    int last = -1;
+    for (uint32_t i = 0; i < sc.n_spheres; ++i) {
+        const SphereDev s = sph[i];
+        const float th = sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r);
+        if (th > 0.f && th < nearest) {
+            nearest = th;
+            if (s.ex != 0.f || s.ey != 0.f || s.ez != 0.f) r.Le = V3(s.ex, s.ey, s.ez);
+            last = (int)i;
+        }
+    }
     if (r.material) {
-        nearest = bvh_t;
         V3 hp = o + d * bvh_t; // bvh.cpp:140
         const TriRec T = load_tri(sc.tris_orig + tri_id);
         float w1, w2;
@@ -457,33 +497,17 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
         float w0 = 1 - w1 - w2;
         const float4* sp4 = reinterpret_cast<const float4*>(sc.shade + tri_id);
         const float4 s0 = __ldg(sp4), s1 = __ldg(sp4 + 1), s2 = __ldg(sp4 + 2), s3 = __ldg(sp4 + 3);
-        V3 n = V3(s0.x, s0.y, s0.z) * w0 + V3(s1.x, s1.y, s1.z) * w1 + V3(s2.x, s2.y, s2.z) * w2; // triangle.cpp:80
         r.uv0 = s0.w * w0 + s2.w * w1 + s3.y * w2; // uv0.x, uv1.x, uv2.x  (triangle.cpp:83)
         r.uv1 = s1.w * w0 + s3.x * w1 + s3.z * w2; // uv0.y, uv1.y, uv2.y
-        r.N = normalize(-n);                        // triangle.cpp:86, meshEngine.cpp:369
-    }
-    // meshEngine.cpp:377-500: fixed order, accept 0 < ts < nearest. The solves do not depend on each other, only the accept
-    // chain does: for the reference's eight spheres they are issued together so that the eight fp64 sqrt chains overlap.
-    auto accept = [&](const SphereDev& s, float th) {
-        if (th > 0.f && th < nearest) {
-            nearest = th;
-            if (s.ex != 0.f || s.ey != 0.f || s.ez != 0.f) r.Le = V3(s.ex, s.ey, s.ez);
-            V3 nn = normalize(o + (d * nearest) - V3(s.nx, s.ny, s.nz));
-            r.N = (s.flags & VMN_SPH_FLIP_NORMAL) ? -nn : nn;
+        if (last < 0) {
+            V3 n = V3(s0.x, s0.y, s0.z) * w0 + V3(s1.x, s1.y, s1.z) * w1 + V3(s2.x, s2.y, s2.z) * w2; // triangle.cpp:80
+            r.N = normalize(-n);                    // triangle.cpp:86, meshEngine.cpp:369
         }
-    };
-#if VMN_SPH_UNROLL
-    if (sc.n_spheres == 8u) {
-        float th[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) th[i] = sphere_intersect(o, d, V3(sph[i].cx, sph[i].cy, sph[i].cz), sph[i].r);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) accept(sph[i], th[i]);
-    } else
-#endif
-    for (uint32_t i = 0; i < sc.n_spheres; ++i) {
-        const SphereDev s = sph[i];
-        accept(s, sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r));
+    }
+    if (last >= 0) {
+        const SphereDev s = sph[last];
+        V3 nn = normalize(o + (d * nearest) - V3(s.nx, s.ny, s.nz));
+        r.N = (s.flags & VMN_SPH_FLIP_NORMAL) ? -nn : nn;
     }
     r.P = o + (d * nearest);
     r.dist = nearest;

@@ -359,6 +359,19 @@ __global__ void k_resolve(const float4* __restrict__ film, float* __restrict__ o
     o[4] = f.w;
 }
 
+// Camera::saveFrame's conversion loop (camera.cpp:138-175, RGBAZ): floor(x * 255) per channel of the resolved pixel, depth = samples
+__global__ void k_pack_rgba8(const float4* __restrict__ film, uchar4* __restrict__ rgba, float* __restrict__ depth, uint64_t npix) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 f = film[p];
+    float r = 0.f, g = 0.f, b = 0.f, a = 0.f;
+    if (f.w != 0.f) {
+        r = fmaxf(fminf(f.x / f.w, 1.f), 0.f); g = fmaxf(fminf(f.y / f.w, 1.f), 0.f); b = fmaxf(fminf(f.z / f.w, 1.f), 0.f); a = 1.f;
+    }
+    rgba[p] = make_uchar4((unsigned char)floorf(r * 255), (unsigned char)floorf(g * 255), (unsigned char)floorf(b * 255), (unsigned char)floorf(a * 255));
+    if (depth) depth[p] = f.w;
+}
+
 __global__ void k_camera_rays(CamDev cam, const uint64_t* __restrict__ pixel, const uint32_t* __restrict__ sx, const uint32_t* __restrict__ sy,
                               const float* __restrict__ jx, const float* __restrict__ jy, uint64_t n, float4* __restrict__ out) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -504,6 +517,13 @@ vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_
 vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix) {
     if (npix == 0) return VMN_OK;
     k_resolve<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), d_rgbaz, npix);
+    VMN_CUDA(c, cudaGetLastError());
+    return VMN_OK;
+}
+
+vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, uint8_t* d_rgba, float* d_depth, uint64_t npix) {
+    if (npix == 0) return VMN_OK;
+    k_pack_rgba8<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<uchar4*>(d_rgba), d_depth, npix);
     VMN_CUDA(c, cudaGetLastError());
     return VMN_OK;
 }

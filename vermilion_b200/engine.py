@@ -30,7 +30,7 @@ EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vm
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
            "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
-           "vmn_film_resolve_device", "vmn_get_stats"]
+           "vmn_film_resolve_device", "vmn_read_image_rgba8", "vmn_get_stats"]
 
 
 class Config(C.Structure):
@@ -116,6 +116,7 @@ def load_library():
     L.vmn_read_image.argtypes = [vp, vp, i32]
     L.vmn_film_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_film_resolve_device.argtypes = [vp, vp, vp]
+    L.vmn_read_image_rgba8.argtypes = [vp, vp, vp]
     L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
     _LIB = L
     return L
@@ -237,6 +238,14 @@ class Engine:
         assert out.dtype == np.float32 and out.shape == shape and out.flags.c_contiguous
         self._chk(self.L.vmn_read_image(self.h, _p(out), layout), "vmn_read_image")
         return out
+
+    def read_image_rgba8(self, want_depth=True):
+        """Camera::saveFrame's 8-bit conversion (camera.cpp:138-175) done on the device: (uint8 [pixels, 4], float32 [pixels] | None)."""
+        npx = self.cam.width * self.cam.height
+        rgba = np.empty((npx, 4), np.uint8)
+        depth = np.empty(npx, np.float32) if want_depth else None
+        self._chk(self.L.vmn_read_image_rgba8(self.h, _p(rgba), _p(depth)), "vmn_read_image_rgba8")
+        return rgba, depth
 
     def film_device(self):
         ptr, n = C.c_void_p(), C.c_uint64()
