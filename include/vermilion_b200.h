@@ -100,8 +100,12 @@ typedef struct {
     uint32_t spp; /* uSamplesPerPixel */
 } vmn_camera;
 
-enum { VMN_MODE_COMPAT = 0, /* the reference estimator exactly: adaptive early-out, r2 = 10*xi, roulette */
-       VMN_MODE_FIXED = 1 };  /* exact spp, r2 = xi, at most max_segments rays per path */
+enum { VMN_MODE_COMPAT = 0, /* PathTracer, the reference estimator exactly: adaptive early-out, r2 = 10*xi, roulette */
+       VMN_MODE_FIXED = 1,  /* PathTracer, exact spp, r2 = xi, at most max_segments rays per path */
+       VMN_MODE_BRUTEFORCE = 2 }; /* BruteForceTracer::Render (core/integrators/integrators.cpp:9-186), the RenderEngine default
+                                   * integrator (renderEngine.cpp:51): point light at (500,1100,2000), normal map = texture slot 0,
+                                   * albedo = texture slot 1, one mirror-direction probe, its own early-out. spp <= 65535 (the
+                                   * reference's uint16_t sample counter never terminates above that). */
 
 typedef struct {
     int32_t mode;           /* VMN_MODE_* */
@@ -114,6 +118,8 @@ typedef struct {
     uint32_t flags;         /* VMN_RENDER_* */
 } vmn_render_params;
 #define VMN_RENDER_ACCUMULATE 1u /* keep the film and add to it (progressive rendering: successive sample slices, FIXED mode) */
+#define VMN_RENDER_BF_SHADOW 2u  /* BRUTEFORCE: enable the shadow ray the reference has commented out (integrators.cpp:108-110):
+                                  * if RayCastCollision(hitLocation, lightDirection) (meshEngine.cpp:196-207) then vNDL *= 0 */
 
 typedef struct {
     uint64_t n_triangles, n_nodes, n_wide_nodes;
@@ -139,7 +145,9 @@ vmn_status vmn_synchronize(vmn_ctx* ctx);
 vmn_status vmn_scene_set_triangles(vmn_ctx* ctx, const float* pos, const float* nrm, const float* uv, uint64_t n);
 vmn_status vmn_scene_set_spheres(vmn_ctx* ctx, const vmn_sphere* spheres, uint32_t n); /* n <= 16; 0 disables */
 void vmn_reference_spheres(vmn_sphere out[8]); /* the eight spheres of meshEngine.cpp:377-500 */
-/* replaces MeshEngine::bindTexture's upload (meshEngine.cpp:85-91); slot 0 is the one Radiance samples */
+/* replaces MeshEngine::bindTexture's upload (meshEngine.cpp:85-91); slot = index in MeshEngine::boundTextures. Slot 0 is the one
+ * Radiance samples (pathtracer.cpp:62-80) and BruteForceTracer's normal map (integrators.cpp:98-106); slot 1 is BruteForceTracer's
+ * albedo (integrators.cpp:141-147). data = NULL unbinds the slot. */
 vmn_status vmn_scene_set_texture(vmn_ctx* ctx, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t c);
 vmn_status vmn_scene_commit(vmn_ctx* ctx); /* builds the BVH on the GPU */
 
@@ -166,13 +174,18 @@ vmn_status vmn_camera_rays(vmn_ctx* ctx, const uint64_t* pixel, const uint32_t* 
 /* replaces PathTracer::Render's pixel loop (pathtracer.cpp:226-324) over this context's share of the frame */
 vmn_status vmn_render(vmn_ctx* ctx, const vmn_render_params* params);
 /* film readback. VMN_FILM_RGBAZ = Camera::mImage layout, 5 floats per pixel (camera.cpp:106-113): clamped rgb, alpha 1,
- * depth = samples taken. VMN_FILM_SUM = raw (sum r, sum g, sum b, n) 4 floats per pixel (for sample-slice all-reduce). */
+ * depth = samples taken (after a BRUTEFORCE render: alpha = hits / samples, depth = distance of the last primary RayCast,
+ * integrators.cpp:176-183). VMN_FILM_SUM = raw (sum r, sum g, sum b, n) 4 floats per pixel (for sample-slice all-reduce). */
 enum { VMN_FILM_RGBAZ = 0, VMN_FILM_SUM = 1 };
 vmn_status vmn_read_image(vmn_ctx* ctx, float* dst, int32_t layout);
 /* device pointer to the raw sum buffer (4 floats per pixel, width*height pixels) for NCCL all-reduce / gather by the host */
 vmn_status vmn_film_device(vmn_ctx* ctx, float** d_sum, uint64_t* n_floats);
 /* resolve an (externally reduced) sum buffer already on the device into RGBAZ on the host */
 vmn_status vmn_film_resolve_device(vmn_ctx* ctx, const float* d_sum, float* dst_rgbaz);
+
+/* BRUTEFORCE film: device pointer to the second accumulation plane, 2 floats per pixel (sum alpha, depth of the last primary
+ * RayCast), which a multi-GPU host reduces together with vmn_film_device's plane (tiles sum with zeros). */
+vmn_status vmn_film_aux_device(vmn_ctx* ctx, float** d_aux, uint64_t* n_floats);
 
 /* replaces the 32f -> 8-bit conversion loop of Camera::saveFrame (camera.cpp:138-175, RGBAZ case): rgba8[4*p+k] =
  * (unsigned char)floor(rgbaz[5*p+k] * 255), depth[p] = rgbaz[5*p+4]. Packed on the device: 8 bytes per pixel cross PCIe instead

@@ -25,10 +25,15 @@
  *    (pathtracer.cpp:231); ref_render_seeded restates that loop (and only that
  *    loop) with a per-pixel seeded std::mt19937_64 and calls the reference's own
  *    Radiance(). ref_render_pathtracer calls the real PathTracer::Render.
+ *  - BruteForceTracer::Render seeds its shared std::mt19937 with time(0) (integrators.cpp:30). The library is
+ *    linked with -Wl,--wrap=time (oracle/Makefile), so that the reference object's call lands in __wrap_time
+ *    below, which returns a caller-chosen value while ref_render_bruteforce runs (and the real time otherwise).
+ *    The source is untouched; with one OpenMP thread the real Render is then reproducible.
  */
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <ctime>
 #include <cmath>
 #include <random>
 #include <string>
@@ -51,6 +56,13 @@
 
 // The reference's own bounce loop, external linkage (pathtracer.cpp:21)
 glm::vec4 Radiance(Vermilion::MeshEngine* mEng, glm::vec3 rStart, glm::vec3 rDir, std::mt19937_64& mtRanEngine);
+
+static long g_fixed_time = 0; // != 0: what the reference's time(0) returns (integrators.cpp:30)
+extern "C" time_t __real_time(time_t*);
+extern "C" time_t __wrap_time(time_t* t) {
+    if (g_fixed_time) { if (t) *t = (time_t)g_fixed_time; return (time_t)g_fixed_time; }
+    return __real_time(t);
+}
 
 namespace {
 
@@ -393,6 +405,26 @@ void ref_render_seeded(const ref_scene* s, const ref_camera_settings* cs, int mo
     }
     for (uint64_t p = p0; p < p1; ++p) memcpy(image + 5 * p, cam->mImage + 5 * p, 5 * sizeof(float));
     delete cam;
+}
+
+/* The real BruteForceTracer::Render through the Integrator interface (integrators.cpp:9-186) with its time(0) seed
+ * pinned to `seed` (see __wrap_time). threads = 1 makes it deterministic (pixels draw from the shared engine in order);
+ * more threads race on the engine exactly as the reference does. image: 5 floats per pixel. Returns seconds. */
+double ref_render_bruteforce(const ref_scene* s, const ref_camera_settings* cs, uint64_t seed, float* image, int threads) {
+    Vermilion::Camera* cam = make_camera(cs);
+    std::vector<Vermilion::Camera*> cams{cam};
+    Vermilion::Integrator* integ = new Vermilion::BruteForceTracer();
+    int saved = omp_get_max_threads();
+    omp_set_num_threads(clamp_threads(threads));
+    g_fixed_time = (long)seed;
+    double t0 = omp_get_wtime();
+    { Quiet q; integ->Render(cams, s->mesh); }
+    double t1 = omp_get_wtime();
+    g_fixed_time = 0;
+    omp_set_num_threads(saved);
+    memcpy(image, cam->mImage, sizeof(float) * 5 * (size_t)cam->RenderTargetSize);
+    delete integ; delete cam;
+    return t1 - t0;
 }
 
 /* the reference MeshEngine of a scene, for oracle/adapter_harness.cpp (the Integrator adapter under test) */

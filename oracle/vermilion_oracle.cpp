@@ -571,6 +571,102 @@ uint64_t render_pixel(const orc_scene& sc, const orc_camera& cam, const M4& M, i
     return nrays;
 }
 
+// ----------------------------------------------------------------------------
+// BruteForceTracer::Render (integrators.cpp:9-186): direct light from a point light,
+// optional normal-map perturbation, one mirror-direction probe, its own early-out.
+// ----------------------------------------------------------------------------
+// std::mt19937 exactly as integrators.cpp:30,35 uses it: ONE engine shared by all pixels
+// (the reference races on it under OpenMP; with one thread the pixels draw in order),
+// uniform_real_distribution<float>(0, 0.5).
+struct RngMt32Shared {
+    std::mt19937& eng;
+    explicit RngMt32Shared(std::mt19937& e) : eng(e) {}
+    void begin_sample(uint32_t) {}
+    float jitter() { std::uniform_real_distribution<float> d(0, 0.5); return d(eng); }
+};
+
+// integrators.cpp:170: `abs` there resolves to ::abs(int) (no float overload is visible in that TU), so the float
+// sum is truncated to int first. x86 cvttss2si returns INT_MIN for NaN / out-of-range, and abs(INT_MIN) stays INT_MIN.
+inline float abs_via_int(float x) {
+    int32_t i = (std::fabs(x) < 2147483648.f) ? (int32_t)x : INT32_MIN;
+    uint32_t a = i < 0 ? 0u - (uint32_t)i : (uint32_t)i;
+    return (float)(int32_t)a;
+}
+
+inline float std_min(float a, float b) { return (b < a) ? b : a; } // std::min(a, b)
+inline float std_max(float a, float b) { return (a < b) ? b : a; } // std::max(a, b)
+
+template <class Rng>
+uint64_t render_pixel_bf(const orc_scene& sc, const orc_camera& cam, const M4& M, uint64_t p, uint32_t flags, Rng& rng, float* px5,
+                         uint32_t* samples_taken) {
+    const V3 lightLocation(500, 1100, 2000); // :16
+    uint64_t nrays = 0;
+    V4 accum{0, 0, 0, 0}, last{0, 0, 0, 0}, cur{0, 0, 0, 0};
+    uint32_t nTotalSamples = 0;
+    float hitDistance = 0.f; // uninitialised in the reference when spp == 0; every RayCast call writes it
+    for (uint16_t sample = 0; sample < cam.spp; ++sample) { // :59
+        ++nTotalSamples;
+        rng.begin_sample(sample);
+        float jx = rng.jitter();
+        float homogenousX = ((float(p % cam.width) + jx - 0.25) / cam.width) * 2 - 1; // :65
+        float jy = rng.jitter();
+        float homogenousY = ((float(p / cam.width) + jy - 0.25) / cam.height) * 2 - 1; // :66
+        float cameraBackXCm = homogenousX * cam.sensor_x * 0.5; // :73
+        float cameraBackYCm = homogenousY * cam.sensor_y * 0.5;
+        float g[4] = {cameraBackXCm, -cameraBackYCm, -cam.dist_to_film, 1.0f};
+        float rd[4];
+        for (int r = 0; r < 4; ++r) rd[r] = (M.m[0][r] * g[0] + M.m[1][r] * g[1]) + (M.m[2][r] * g[2] + M.m[3][r] * g[3]);
+        V3 dir = normalize(V3(rd[0] / rd[3], rd[1] / rd[3], rd[2] / rd[3]));
+        RayCastOut h = ray_cast(sc, V3(cam.position[0], cam.position[1], cam.position[2]), dir); // :81
+        ++nrays;
+        hitDistance = h.dist;
+        if (h.hit) {
+            V3 lightDirection = normalize(lightLocation - h.P); // :83-84
+            V3 hitNormal = h.N;
+            float vNDL = dot(lightDirection, normalize(hitNormal)); // :88
+            if (sc.textures.size() > 0) { // :98-106
+                float n4[4];
+                texture_sample(sc.textures[0], h.uv, n4);
+                hitNormal = hitNormal + V3(n4[0], n4[1], n4[2]);
+                vNDL = dot(lightDirection, normalize(hitNormal));
+            }
+            if (flags & ORC_BF_SHADOW) { // the commented-out :109-110, RayCastCollision semantics (meshEngine.cpp:196-207)
+                Ray sr(h.P, lightDirection);
+                float st;
+                uint32_t id = sc.bvh.closest<false>(sc.tris, sr, &st, nullptr, nullptr);
+                ++nrays;
+                if (id != 0xFFFFFFFFu && st > 1e-3) vNDL *= 0.00f;
+            }
+            V3 secondBounceDirection = -lightDirection - (hitNormal * 2.f) * dot(hitNormal, -lightDirection); // :119
+            RayCastOut h2 = ray_cast(sc, h.P, secondBounceDirection); // :121 (its outputs only feed `resp`, which is never used)
+            ++nrays;
+            if (!h2.hit) { vNDL *= 0.9f; vNDL += 0.1f; } // :133-137
+            if (sc.textures.size() > 1) { // :141-147
+                float c4[4];
+                texture_sample(sc.textures[1], h.uv, c4);
+                cur = V4{c4[0] * vNDL, c4[1] * vNDL, c4[2] * vNDL, 1.0f};
+            } else {
+                cur = V4{0.890196078f * vNDL, 0.258823529f * vNDL, 0.203921569f * vNDL, 1.0f}; // :150-155
+            }
+            accum.x += cur.x; accum.y += cur.y; accum.z += cur.z; accum.w += cur.w; // :158
+        }
+        const float fn = (float)nTotalSamples;
+        if (nTotalSamples > 2) { // :167-172
+            last.x -= accum.x / fn; last.y -= accum.y / fn; last.z -= accum.z / fn; last.w -= accum.w / fn;
+            float mag = abs_via_int(last.x + last.y + last.z + last.w);
+            if (mag < 0.001f) break;
+        }
+        last = V4{accum.x / fn, accum.y / fn, accum.z / fn, accum.w / fn}; // :173
+    }
+    px5[0] = std_max(std_min(accum.x / nTotalSamples, 1.f), 0.f); // :177-181
+    px5[1] = std_max(std_min(accum.y / nTotalSamples, 1.f), 0.f);
+    px5[2] = std_max(std_min(accum.z / nTotalSamples, 1.f), 0.f);
+    px5[3] = accum.w / nTotalSamples;
+    px5[4] = hitDistance;
+    if (samples_taken) *samples_taken = nTotalSamples;
+    return nrays;
+}
+
 inline int clamp_threads(int t) { int m = omp_get_max_threads(); return (t <= 0 || t > m) ? m : t; }
 
 } // namespace
@@ -599,6 +695,10 @@ void orc_scene_destroy(orc_scene* s) { delete s; }
 void orc_scene_set_texture(orc_scene* s, const float* data, uint32_t w, uint32_t h, uint32_t c) {
     Texture t; t.w = w; t.h = h; t.c = c; t.data.assign(data, data + (size_t)w * h * c);
     s->textures.clear(); s->textures.push_back(std::move(t));
+}
+void orc_scene_add_texture(orc_scene* s, const float* data, uint32_t w, uint32_t h, uint32_t c) { // MeshEngine::bindTexture appends (meshEngine.cpp:91)
+    Texture t; t.w = w; t.h = h; t.c = c; t.data.assign(data, data + (size_t)w * h * c);
+    s->textures.push_back(std::move(t));
 }
 void orc_scene_set_spheres(orc_scene* s, int enabled) { s->spheres = enabled != 0; }
 void orc_scene_stats(const orc_scene* s, uint32_t* n_nodes, uint32_t* n_leafs) {
@@ -701,6 +801,26 @@ uint64_t orc_render(const orc_scene* s, const orc_camera* cam, int mode, int rng
         float* raw = raw_sum ? raw_sum + 4 * (size_t)p : nullptr;
         if (rng_kind == ORC_RNG_MT64) { RngMt64 rng(seed + (uint64_t)p); total += render_pixel(*s, *cam, M, mode, (uint64_t)p, s0, s1, max_segments, rng, px, raw); }
         else { RngPhilox rng(seed, (uint64_t)p); total += render_pixel(*s, *cam, M, mode, (uint64_t)p, s0, s1, max_segments, rng, px, raw); }
+    }
+    return total;
+}
+
+uint64_t orc_render_bruteforce(const orc_scene* s, const orc_camera* cam, int rng_kind, uint64_t seed, uint32_t flags, uint64_t p0,
+                                uint64_t p1, float* image, uint32_t* samples_taken, int threads) {
+    M4 M = camera_matrix(*cam);
+    uint64_t total = 0;
+    if (rng_kind == ORC_RNG_MT32_SHARED) { // sequential by construction: one engine, pixels in order
+        std::mt19937 eng((uint32_t)seed);
+        RngMt32Shared rng(eng);
+        for (uint64_t p = p0; p < p1; ++p)
+            total += render_pixel_bf(*s, *cam, M, p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr);
+        return total;
+    }
+    threads = clamp_threads(threads);
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) reduction(+ : total)
+    for (int64_t p = (int64_t)p0; p < (int64_t)p1; ++p) {
+        RngPhilox rng(seed, (uint64_t)p);
+        total += render_pixel_bf(*s, *cam, M, (uint64_t)p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr);
     }
     return total;
 }

@@ -8,7 +8,8 @@
  * The oracle is a plain C++ restatement (no glm, no Assimp) of the reference
  * path: core/accelerators/{bvh,bbox,triangle}.cpp, core/engines/meshEngine.cpp
  * (RayCast, sphereIntersect, VermiTexture::Sample) and
- * core/integrators/pathtracer.cpp (Radiance, PathTracer::Render). Each
+ * core/integrators/pathtracer.cpp (Radiance, PathTracer::Render) and
+ * core/integrators/integrators.cpp (BruteForceTracer::Render). Each
  * function in vermilion_oracle.cpp cites the reference file:line it follows.
  *
  * Parity status: PINNED — against the reference's own code compiled from
@@ -63,7 +64,8 @@ typedef struct {
 } orc_camera;
 
 enum { ORC_MODE_COMPAT = 0, ORC_MODE_FIXED = 1 };
-enum { ORC_RNG_MT64 = 0, ORC_RNG_PHILOX = 1 };
+enum { ORC_RNG_MT64 = 0, ORC_RNG_PHILOX = 1, ORC_RNG_MT32_SHARED = 2 };
+#define ORC_BF_SHADOW 1u /* BruteForceTracer with the commented-out shadow test of integrators.cpp:109-110 enabled */
 
 typedef struct orc_scene orc_scene;
 
@@ -72,7 +74,8 @@ typedef struct orc_scene orc_scene;
  * running face index of MeshEngine::createBVH (meshEngine.cpp:660-717). */
 orc_scene* orc_scene_create(const float* pos, const float* nrm, const float* uv, uint64_t ntri, uint32_t leaf_size);
 void orc_scene_destroy(orc_scene*);
-void orc_scene_set_texture(orc_scene*, const float* data, uint32_t w, uint32_t h, uint32_t c);
+void orc_scene_set_texture(orc_scene*, const float* data, uint32_t w, uint32_t h, uint32_t c); /* replaces all bound textures by this one */
+void orc_scene_add_texture(orc_scene*, const float* data, uint32_t w, uint32_t h, uint32_t c); /* appends, as MeshEngine::bindTexture does */
 /* enable / disable the 8 hard-coded spheres of RayCast (default: enabled) */
 void orc_scene_set_spheres(orc_scene*, int enabled);
 void orc_scene_stats(const orc_scene*, uint32_t* n_nodes, uint32_t* n_leafs);
@@ -107,6 +110,14 @@ void orc_camera_ray(const orc_camera*, uint64_t p, uint32_t sx, uint32_t sy, flo
 uint64_t orc_render(const orc_scene*, const orc_camera*, int mode, int rng_kind, uint64_t seed,
                     uint64_t p0, uint64_t p1, uint32_t s0, uint32_t s1, uint32_t max_segments,
                     float* image, float* raw_sum, int threads);
+
+/* BruteForceTracer::Render pixel loop (integrators.cpp:21-185). rng_kind MT32_SHARED: one std::mt19937((uint32)seed)
+ * shared by all pixels, drawn in pixel order (what the reference does with one OpenMP thread; its seed is time(0),
+ * integrators.cpp:30). PHILOX: stream (seed, pixel, sample), draws 0 and 1. image: 5 floats per pixel = clamped rgb,
+ * alpha = hits / samples, depth = distance of the last primary RayCast (integrators.cpp:176-183). samples_taken
+ * (optional): nTotalSamples per pixel. Returns the number of BVH queries made. */
+uint64_t orc_render_bruteforce(const orc_scene*, const orc_camera*, int rng_kind, uint64_t seed, uint32_t flags, uint64_t p0,
+                               uint64_t p1, float* image, uint32_t* samples_taken, int threads);
 
 /* Counter-based RNG shared by the oracle's PHILOX mode and the GPU path:
  * Philox4x32-10, key (seed_lo, seed_hi), counter (pixel_lo, pixel_hi, sample, draw/4). */

@@ -21,7 +21,8 @@ RAYCAST = np.dtype([("P", "<f4", 3), ("dist", "<f4"), ("N", "<f4", 3), ("flags",
 assert RAY.itemsize == 32 and HIT.itemsize == 16 and RAYCAST.itemsize == 64
 RC_HIT, RC_MATERIAL = 1, 2
 MODE_COMPAT, MODE_FIXED = 0, 1
-RNG_MT64, RNG_PHILOX = 0, 1
+RNG_MT64, RNG_PHILOX, RNG_MT32_SHARED = 0, 1, 2
+BF_SHADOW = 1
 MISS = 0xFFFFFFFF
 
 
@@ -100,6 +101,10 @@ class Oracle:
             L.orc_render.restype = C.c_uint64
             L.orc_render.argtypes = [C.c_void_p, C.POINTER(OrcCamera), C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64,
                                      C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+            L.orc_scene_add_texture.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+            L.orc_render_bruteforce.restype = C.c_uint64
+            L.orc_render_bruteforce.argtypes = [C.c_void_p, C.POINTER(OrcCamera), C.c_int, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64,
+                                                C.c_void_p, C.c_void_p, C.c_int]
             L.orc_philox.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
             L.orc_max_threads.restype = C.c_int
             cls._lib = L
@@ -124,6 +129,20 @@ class Oracle:
         tex = np.ascontiguousarray(tex, np.float32)
         h, w, c = tex.shape
         self.lib().orc_scene_set_texture(self.h, _p(tex), w, h, c)
+
+    def add_texture(self, tex):
+        tex = np.ascontiguousarray(tex, np.float32)
+        h, w, c = tex.shape
+        self.lib().orc_scene_add_texture(self.h, _p(tex), w, h, c)
+
+    def render_bruteforce(self, cam, rng=RNG_PHILOX, seed=1, flags=0, p0=0, p1=None, threads=0):
+        """BruteForceTracer::Render restated: (image[npix,5], samples_taken[npix], BVH queries)"""
+        npx = cam.width * cam.height
+        p1 = npx if p1 is None else p1
+        img = np.zeros((npx, 5), np.float32)
+        taken = np.zeros(npx, np.uint32)
+        n = self.lib().orc_render_bruteforce(self.h, C.byref(cam), rng, seed, flags, p0, p1, _p(img), _p(taken), threads)
+        return img, taken, n
 
     def stats(self):
         a, b = C.c_uint32(), C.c_uint32()
@@ -219,6 +238,8 @@ class Ref:
             L.ref_render_pathtracer.argtypes = [C.c_void_p, C.POINTER(RefCameraSettings), C.c_void_p, C.c_int]
             L.ref_render_seeded.argtypes = [C.c_void_p, C.POINTER(RefCameraSettings), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64,
                                             C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
+            L.ref_render_bruteforce.restype = C.c_double
+            L.ref_render_bruteforce.argtypes = [C.c_void_p, C.POINTER(RefCameraSettings), C.c_uint64, C.c_void_p, C.c_int]
             L.ref_build_flags.restype = C.c_char_p
             L.ref_max_threads.restype = C.c_int
             cls._libs[variant] = L
@@ -276,6 +297,12 @@ class Ref:
     def render_pathtracer(self, cs, threads=0):
         img = np.zeros((cs.width * cs.height, 5), np.float32)
         secs = self.L.ref_render_pathtracer(self.h, C.byref(cs), _p(img), threads)
+        return img, secs
+
+    def render_bruteforce(self, cs, seed=1, threads=1):
+        """the real BruteForceTracer::Render with its time(0) seed pinned; threads=1 is deterministic"""
+        img = np.zeros((cs.width * cs.height, 5), np.float32)
+        secs = self.L.ref_render_bruteforce(self.h, C.byref(cs), seed, _p(img), threads)
         return img, secs
 
     def render_seeded(self, cs, mode=MODE_COMPAT, seed=1, p0=0, p1=None, s0=0, s1=None, max_segments=5, threads=0, want_raw=False):

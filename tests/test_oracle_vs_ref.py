@@ -154,3 +154,43 @@ def test_ofast_variant_is_within_the_stated_tolerance():
     hit = same & (a["tri"] != checker.MISS)
     rel = np.abs(a["t"][hit] - b["t"][hit]) / np.maximum(1.0, np.abs(a["t"][hit]))
     assert rel.max() < 1e-3 and np.quantile(rel, 0.999) < 1e-5
+
+
+# ---- BruteForceTracer::Render (integrators.cpp:9-186) -------------------------------------------------------------------------------
+def bf_textures(kind, seed=3):
+    """(normal map, albedo) for MeshEngine::boundTextures[0..1]; 'hot' albedo values force the early-out past 3 samples"""
+    rng = np.random.default_rng(seed)
+    nmap = (rng.random((8, 8, 3), dtype=np.float32) - np.float32(0.5)) * np.float32(0.6)
+    alb = rng.random((16, 8, 4), dtype=np.float32) * np.float32(60.0 if kind == "hot" else 1.0)
+    return nmap, alb
+
+
+@needs_ref
+@pytest.mark.parametrize("name,textures,zero_normals", [("cornell", 0, False), ("cornell", 1, False), ("cornell", 2, False),
+                                                         ("cornell", "hot", False), ("cornell", 0, True), ("city", 2, False)])
+def test_bruteforce_render_bit_exact(name, textures, zero_normals):
+    """The REAL BruteForceTracer::Render (one OpenMP thread, its time(0) seed pinned through the --wrap=time hook of
+    oracle/ref_harness.cpp) against the restatement drawing from the same shared std::mt19937 in pixel order."""
+    pos, nrm, uv = _scene(name)
+    if zero_normals:
+        nrm = None  # normalize(0) = NaN normals: the abs(int) early-out and std::min/max clamps see NaN
+    cs = checker.camera_settings(72, 56, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 2.8), 12) if name == "cornell" else \
+        checker.camera_settings(72, 56, (-1500, 900, 1800), (-20, 30, 0), 6.0, (3.6, 2.8), 12)
+    ref = checker.Ref(pos, nrm, uv)
+    orc = checker.Oracle(pos, nrm, uv)
+    nmap, alb = bf_textures("hot" if textures == "hot" else "plain")
+    for k in range(2 if textures == "hot" else textures):
+        t = nmap if k == 0 else alb
+        ref.set_texture(t)
+        orc.set_texture(t) if k == 0 else orc.add_texture(t)
+    cam = ref.camera_fields(cs)
+    want, _ = ref.render_bruteforce(cs, seed=77, threads=1)
+    got, taken, nq = orc.render_bruteforce(cam, rng=checker.RNG_MT32_SHARED, seed=77)
+    assert np.array_equal(_bits(got), _bits(want))
+    assert (got[:, 3] > 0).mean() > 0.9  # the room's wall spheres catch every primary ray
+    if textures == "hot":
+        assert taken.max() > 3  # the early-out is not always the third sample
+    else:
+        assert (taken == 3).all()  # integrators.cpp:170 calls ::abs(int): any |delta| < 1 stops the pixel at its third sample
+    if zero_normals:
+        assert np.isnan(got[:, :3]).any()

@@ -106,7 +106,7 @@ void vmn_destroy(vmn_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     pool_destroy(c);
     for (DevBuf* b : {&c->pos, &c->nrm, &c->uv, &c->tris, &c->tris_sorted, &c->tris_orig, &c->shade, &c->wide, &c->b_min, &c->b_max,
-                      &c->b_child, &c->spheres, &c->tex, &c->film, &c->q_in, &c->q_out, &c->counters})
+                      &c->b_child, &c->spheres, &c->tex, &c->tex1, &c->film, &c->film_aux, &c->q_in, &c->q_out, &c->counters})
         dev_free(*b);
     for (DevBuf& b : c->build_scratch) dev_free(b);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -191,16 +191,29 @@ void vmn_reference_spheres(vmn_sphere out[8]) {
     set(7, 0.f, 0.f, (float)(S - 2000), R, 0, 0, 0, 0u, 0.f, 0.f, (float)(S - 2000));
 }
 
+static void scene_bind_textures(vmn_ctx* c) {
+    c->scene.tex = c->have_tex ? c->tex.as<float>() : nullptr;
+    c->scene.tex_w = c->tex_w; c->scene.tex_h = c->tex_h; c->scene.tex_c = c->tex_c;
+    c->scene.tex1 = c->have_tex1 ? c->tex1.as<float>() : nullptr;
+    c->scene.tex1_w = c->tex1_w; c->scene.tex1_h = c->tex1_h; c->scene.tex1_c = c->tex1_c;
+}
+
 vmn_status vmn_scene_set_texture(vmn_ctx* c, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t ch) {
     CHECK_CTX(c);
-    if (slot != 0) return fail(c, VMN_ERR_INVALID, "only texture slot 0 is sampled (pathtracer.cpp:62-80)");
-    if (!data || !w || !h || ch < 1 || ch > 4) return fail(c, VMN_ERR_INVALID, "bad texture");
+    if (slot > 1) return fail(c, VMN_ERR_INVALID, "texture slot %u: only slots 0 (pathtracer.cpp:62-80, integrators.cpp:98-106) and 1 (integrators.cpp:141-147) are sampled", slot);
+    if (!data) { // unbind
+        if (slot == 0) c->have_tex = false; else c->have_tex1 = false;
+        scene_bind_textures(c);
+        return VMN_OK;
+    }
+    if (!w || !h || ch < 1 || ch > 4) return fail(c, VMN_ERR_INVALID, "bad texture");
     SET_DEVICE(c);
-    vmn_status s = upload(c, c->tex, data, sizeof(float) * (size_t)w * h * ch);
+    vmn_status s = upload(c, slot == 0 ? c->tex : c->tex1, data, sizeof(float) * (size_t)w * h * ch);
     if (s != VMN_OK) return s;
     VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->tex_w = w; c->tex_h = h; c->tex_c = ch;
-    c->scene.tex = c->tex.as<float>(); c->scene.tex_w = w; c->scene.tex_h = h; c->scene.tex_c = ch;
+    if (slot == 0) { c->tex_w = w; c->tex_h = h; c->tex_c = ch; c->have_tex = true; }
+    else { c->tex1_w = w; c->tex1_h = h; c->tex1_c = ch; c->have_tex1 = true; }
+    scene_bind_textures(c);
     return VMN_OK;
 }
 
@@ -210,7 +223,7 @@ vmn_status vmn_scene_commit(vmn_ctx* c) {
     vmn_status s = build_bvh(c);
     if (s != VMN_OK) return s;
     c->scene.n_spheres = c->n_spheres;
-    c->scene.tex = c->tex.as<float>(); c->scene.tex_w = c->tex_w; c->scene.tex_h = c->tex_h; c->scene.tex_c = c->tex_c;
+    scene_bind_textures(c);
     // the staged arrays stay allocated (reused by the next vmn_scene_set_triangles); they are 96 B/triangle
     c->committed = true;
     return VMN_OK;
@@ -323,6 +336,7 @@ vmn_status vmn_camera_set(vmn_ctx* c, const vmn_camera* cam) {
         c->film_pixels = npix;
     }
     VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
+    c->film_bf = false;
     return VMN_OK;
 }
 
@@ -357,8 +371,10 @@ vmn_status vmn_render(vmn_ctx* c, const vmn_render_params* p) {
     NEED_COMMIT(c);
     if (!p) return fail(c, VMN_ERR_INVALID, "null params");
     if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
-    if (p->mode != VMN_MODE_COMPAT && p->mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "bad mode %d", p->mode);
+    if (p->mode != VMN_MODE_COMPAT && p->mode != VMN_MODE_FIXED && p->mode != VMN_MODE_BRUTEFORCE) return fail(c, VMN_ERR_INVALID, "bad mode %d", p->mode);
     SET_DEVICE(c);
+    if (p->mode == VMN_MODE_BRUTEFORCE) return render_bruteforce(c, p);
+    c->film_bf = false;
     return render_frame(c, p);
 }
 
@@ -370,6 +386,15 @@ vmn_status vmn_film_device(vmn_ctx* c, float** d_sum, uint64_t* n_floats) {
     return VMN_OK;
 }
 
+vmn_status vmn_film_aux_device(vmn_ctx* c, float** d_aux, uint64_t* n_floats) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (!c->film_bf) return fail(c, VMN_ERR_STATE, "the film does not hold a BRUTEFORCE render");
+    if (d_aux) *d_aux = c->film_aux.as<float>();
+    if (n_floats) *n_floats = 2 * c->film_pixels;
+    return VMN_OK;
+}
+
 vmn_status vmn_film_resolve_device(vmn_ctx* c, const float* d_sum, float* dst) {
     CHECK_CTX(c);
     if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
@@ -377,7 +402,7 @@ vmn_status vmn_film_resolve_device(vmn_ctx* c, const float* d_sum, float* dst) {
     SET_DEVICE(c);
     vmn_status s = dev_reserve(c, c->q_out, 20 * c->film_pixels);
     if (s != VMN_OK) return s;
-    if ((s = film_resolve(c, d_sum, c->q_out.as<float>(), c->film_pixels)) != VMN_OK) return s;
+    if ((s = film_resolve(c, d_sum, c->film_bf ? c->film_aux.as<float>() : nullptr, c->q_out.as<float>(), c->film_pixels)) != VMN_OK) return s;
     return fetch(c, dst, 20 * c->film_pixels);
 }
 
@@ -405,7 +430,7 @@ vmn_status vmn_read_image_rgba8(vmn_ctx* c, uint8_t* rgba8, float* depth) {
     if (s != VMN_OK) return s;
     uint8_t* d_rgba = c->q_out.as<uint8_t>();
     float* d_depth = reinterpret_cast<float*>(d_rgba + 4 * npix);
-    if ((s = film_pack_rgba8(c, c->film.as<float>(), d_rgba, depth ? d_depth : nullptr, npix)) != VMN_OK) return s;
+    if ((s = film_pack_rgba8(c, c->film.as<float>(), c->film_bf ? c->film_aux.as<float>() : nullptr, d_rgba, depth ? d_depth : nullptr, npix)) != VMN_OK) return s;
     VMN_CUDA(c, cudaMemcpyAsync(rgba8, d_rgba, 4 * npix, cudaMemcpyDeviceToHost, c->stream));
     if (depth) VMN_CUDA(c, cudaMemcpyAsync(depth, d_depth, 4 * npix, cudaMemcpyDeviceToHost, c->stream));
     VMN_CUDA(c, cudaStreamSynchronize(c->stream));

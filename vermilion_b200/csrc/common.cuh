@@ -98,6 +98,8 @@ struct SceneDev {
     uint32_t n_spheres;
     const float* tex;        // texture slot 0 or nullptr
     uint32_t tex_w, tex_h, tex_c;
+    const float* tex1;       // texture slot 1 (BruteForceTracer's albedo) or nullptr
+    uint32_t tex1_w, tex1_h, tex1_c;
 };
 
 struct SphereDev { float cx, cy, cz, r; float ex, ey, ez; uint32_t flags; float nx, ny, nz, pad; };

@@ -37,9 +37,10 @@ struct vmn_ctx {
 
     // built scene
     vmn::DevBuf tris, tris_sorted, tris_orig, shade, wide, b_min, b_max, b_child;
-    vmn::DevBuf spheres, tex;
+    vmn::DevBuf spheres, tex, tex1;
     vmn::DevBuf build_scratch[15]; // bvh_build.cu, grow-only
-    uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0;
+    uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0, tex1_w = 0, tex1_h = 0, tex1_c = 0;
+    bool have_tex = false, have_tex1 = false;
     uint64_t n_wide = 0;
     vmn::SceneDev scene{};
 
@@ -48,6 +49,8 @@ struct vmn_ctx {
     bool have_cam = false;
     float cam_m[16];
     vmn::DevBuf film;      // float4 (sum r,g,b, n) per pixel
+    vmn::DevBuf film_aux;  // BRUTEFORCE only: float2 (sum alpha, last primary hit distance) per pixel
+    bool film_bf = false;  // the film holds a BRUTEFORCE render (resolve: alpha = sum alpha / n, depth = distance)
     uint64_t film_pixels = 0;
 
     // wavefront pool
@@ -89,8 +92,10 @@ vmn_status launch_radiance(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint64
 vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_t* d_sx, const uint32_t* d_sy, const float* d_jx,
                               const float* d_jy, uint64_t n, vmn_ray* d_out);
 vmn_status render_frame(vmn_ctx* c, const vmn_render_params* p);
-vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix);
-vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, uint8_t* d_rgba, float* d_depth, uint64_t npix);
+vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* p);
+// d_aux: BRUTEFORCE second plane or nullptr (PathTracer film: alpha 1, depth = samples)
+vmn_status film_resolve(vmn_ctx* c, const float* d_sum, const float* d_aux, float* d_rgbaz, uint64_t npix);
+vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, const float* d_aux, uint8_t* d_rgba, float* d_depth, uint64_t npix);
 void pool_destroy(vmn_ctx* c);
 void camera_matrix(const vmn_camera& cam, float m[16]);
 

@@ -68,6 +68,7 @@ struct PathPool {
     DevBuf meta;      // uint2 per slot: (draw counter, depth | segs<<16)
     DevBuf ctl;       // uint32 counters: [0..1] queue counts, [8..] claim counters (unsigned long long)
     DevBuf cstate;    // COMPAT per-local-pixel stratum state
+    DevBuf bf_last;   // BRUTEFORCE per-local-pixel lastSampleColour (float4)
     uint32_t* h_count = nullptr; // pinned
     std::vector<cudaEvent_t> events;
     size_t ev_used = 0;
@@ -76,7 +77,7 @@ struct PathPool {
 void pool_destroy(vmn_ctx* c) {
     PathPool* p = c->pool;
     if (!p) return;
-    for (DevBuf* b : {&p->ray[0], &p->ray[1], &p->hit, &p->radiance, &p->thr, &p->meta, &p->ctl, &p->cstate}) dev_free(*b);
+    for (DevBuf* b : {&p->ray[0], &p->ray[1], &p->hit, &p->radiance, &p->thr, &p->meta, &p->ctl, &p->cstate, &p->bf_last}) dev_free(*b);
     if (p->h_count) cudaFreeHost(p->h_count);
     for (auto e : p->events) cudaEventDestroy(e);
     delete p;
@@ -186,19 +187,22 @@ __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev s
 
 // ---- shade -----------------------------------------------------------------------------------------
 // VermiTexture::Sample (meshEngine.cpp:21-46)
-__device__ __forceinline__ void texture_sample(const SceneDev& sc, float u, float v, float out[4]) {
+__device__ __forceinline__ void texture_sample(const float* __restrict__ tex, uint32_t tw, uint32_t th, uint32_t tc, float u, float v, float out[4]) {
     float sx = u - floorf(u), sy = v - floorf(v);
-    uint32_t mx = (uint32_t)roundf(sx * (float)(sc.tex_w - 1u));
-    uint32_t my = (uint32_t)roundf(sy * (float)(sc.tex_h - 1u));
-    const float* p = sc.tex + (size_t)(my * sc.tex_w + mx) * sc.tex_c;
+    uint32_t mx = (uint32_t)roundf(sx * (float)(tw - 1u));
+    uint32_t my = (uint32_t)roundf(sy * (float)(th - 1u));
+    const float* p = tex + (size_t)(my * tw + mx) * tc;
     out[0] = out[1] = out[2] = out[3] = 0.f;
-    switch (sc.tex_c) {
+    switch (tc) {
     case 1: out[0] = out[1] = out[2] = out[3] = p[0]; break;
     case 2: out[0] = p[0]; out[1] = p[1]; break;
     case 3: out[0] = p[0]; out[1] = p[1]; out[2] = p[2]; break;
     case 4: out[0] = p[0]; out[1] = p[1]; out[2] = p[2]; out[3] = p[3]; break;
     default: break;
     }
+}
+__device__ __forceinline__ void texture_sample(const SceneDev& sc, float u, float v, float out[4]) {
+    texture_sample(sc.tex, sc.tex_w, sc.tex_h, sc.tex_c, u, v, out);
 }
 
 // cosine-ish hemisphere direction of pathtracer.cpp:155-162 / :175-186 around normal N for incoming rDir
@@ -359,17 +363,46 @@ __global__ void k_resolve(const float4* __restrict__ film, float* __restrict__ o
     o[4] = f.w;
 }
 
-// Camera::saveFrame's conversion loop (camera.cpp:138-175, RGBAZ): floor(x * 255) per channel of the resolved pixel, depth = samples
-__global__ void k_pack_rgba8(const float4* __restrict__ film, uchar4* __restrict__ rgba, float* __restrict__ depth, uint64_t npix) {
+// std::max(std::min(x, 1.f), 0.f) as integrators.cpp:177-179 evaluates it: std::min(a,b) = (b < a) ? b : a, std::max(a,b) = (a < b) ? b : a,
+// so a NaN mean stays NaN (fminf/fmaxf would drop it)
+__device__ __forceinline__ float clamp01_std(float x) {
+    const float m = (1.f < x) ? 1.f : x;
+    return (m < 0.f) ? 0.f : m;
+}
+
+// integrators.cpp:176-183 + camera.cpp:106-113: BRUTEFORCE film (sum rgb, n) + (sum alpha, last primary distance) -> RGBAZ
+__global__ void k_resolve_bf(const float4* __restrict__ film, const float2* __restrict__ aux, float* __restrict__ out, uint64_t npix) {
     const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npix) return;
     const float4 f = film[p];
-    float r = 0.f, g = 0.f, b = 0.f, a = 0.f;
+    const float2 a = aux[p];
+    float* o = out + 5 * p;
+    if (f.w == 0.f) { o[0] = o[1] = o[2] = o[3] = o[4] = 0.f; return; } // pixel not rendered by anyone
+    o[0] = clamp01_std(f.x / f.w);
+    o[1] = clamp01_std(f.y / f.w);
+    o[2] = clamp01_std(f.z / f.w);
+    o[3] = a.x / f.w;
+    o[4] = a.y;
+}
+
+// Camera::saveFrame's conversion loop (camera.cpp:138-175, RGBAZ): floor(x * 255) per channel of the resolved pixel; depth = the
+// resolved pixel's fifth float (samples for PathTracer films, distance for BRUTEFORCE films)
+__global__ void k_pack_rgba8(const float4* __restrict__ film, const float2* __restrict__ aux, uchar4* __restrict__ rgba, float* __restrict__ depth,
+                             uint64_t npix) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 f = film[p];
+    float r = 0.f, g = 0.f, b = 0.f, a = 0.f, z = f.w;
     if (f.w != 0.f) {
-        r = fmaxf(fminf(f.x / f.w, 1.f), 0.f); g = fmaxf(fminf(f.y / f.w, 1.f), 0.f); b = fmaxf(fminf(f.z / f.w, 1.f), 0.f); a = 1.f;
+        if (aux) {
+            const float2 x = aux[p];
+            r = clamp01_std(f.x / f.w); g = clamp01_std(f.y / f.w); b = clamp01_std(f.z / f.w); a = x.x / f.w; z = x.y;
+        } else {
+            r = fmaxf(fminf(f.x / f.w, 1.f), 0.f); g = fmaxf(fminf(f.y / f.w, 1.f), 0.f); b = fmaxf(fminf(f.z / f.w, 1.f), 0.f); a = 1.f;
+        }
     }
     rgba[p] = make_uchar4((unsigned char)floorf(r * 255), (unsigned char)floorf(g * 255), (unsigned char)floorf(b * 255), (unsigned char)floorf(a * 255));
-    if (depth) depth[p] = f.w;
+    if (depth) depth[p] = z;
 }
 
 __global__ void k_camera_rays(CamDev cam, const uint64_t* __restrict__ pixel, const uint32_t* __restrict__ sx, const uint32_t* __restrict__ sy,
@@ -447,27 +480,37 @@ static int extend_grid(vmn_ctx* c, bool count) {
 constexpr uint32_t kMaxClaims = 480;
 constexpr size_t kOffFrame = 4000;
 
-// one extend + shade iteration over queue `cur`; claim counter index `it`
-static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const RoundParams& rp, int cur, uint32_t it, int radiance_query,
-                         StageClock* clk, int grid_extend) {
+// k_extend over queue `cur`; claim counter index `it`
+static vmn_status launch_extend(vmn_ctx* c, PathPool* p, int cur, uint32_t it, StageClock* clk, int grid_extend) {
     uint32_t* qc = p->ctl.as<uint32_t>();
     unsigned long long* claims = reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + 64);
     TravCounters* gcnt = reinterpret_cast<TravCounters*>(p->ctl.as<char>() + kOffFrame);
     unsigned long long* total = reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + kOffFrame + 16);
     const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
-    VMN_CUDA(c, cudaMemsetAsync(qc + (cur ^ 1), 0, 4, c->stream));
     if (clk) clk->begin(ST_EXTEND);
     if (count)
         k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
     else
         k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
-    if (clk) { clk->end(); clk->begin(ST_SHADE); }
+    if (clk) clk->end();
+    ++c->stats.kernel_launches;
+    return VMN_OK;
+}
+
+// one extend + shade iteration over queue `cur`; claim counter index `it`
+static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const RoundParams& rp, int cur, uint32_t it, int radiance_query,
+                         StageClock* clk, int grid_extend) {
+    uint32_t* qc = p->ctl.as<uint32_t>();
+    VMN_CUDA(c, cudaMemsetAsync(qc + (cur ^ 1), 0, 4, c->stream));
+    vmn_status s = launch_extend(c, p, cur, it, clk, grid_extend);
+    if (s != VMN_OK) return s;
+    if (clk) clk->begin(ST_SHADE);
     k_shade<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
                                                          qc + cur, p->ray[cur ^ 1].as<float4>(), qc + (cur ^ 1), p->radiance.as<float4>(),
                                                          p->thr.as<float4>(), p->meta.as<uint2>(), radiance_query);
     if (clk) clk->end();
     VMN_CUDA(c, cudaGetLastError());
-    c->stats.kernel_launches += 2;
+    ++c->stats.kernel_launches;
     return VMN_OK;
 }
 
@@ -514,17 +557,43 @@ vmn_status launch_camera_rays(vmn_ctx* c, const uint64_t* d_pixel, const uint32_
     return VMN_OK;
 }
 
-vmn_status film_resolve(vmn_ctx* c, const float* d_sum, float* d_rgbaz, uint64_t npix) {
+vmn_status film_resolve(vmn_ctx* c, const float* d_sum, const float* d_aux, float* d_rgbaz, uint64_t npix) {
     if (npix == 0) return VMN_OK;
-    k_resolve<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), d_rgbaz, npix);
+    if (d_aux)
+        k_resolve_bf<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<const float2*>(d_aux), d_rgbaz, npix);
+    else
+        k_resolve<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), d_rgbaz, npix);
     VMN_CUDA(c, cudaGetLastError());
     return VMN_OK;
 }
 
-vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, uint8_t* d_rgba, float* d_depth, uint64_t npix) {
+vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, const float* d_aux, uint8_t* d_rgba, float* d_depth, uint64_t npix) {
     if (npix == 0) return VMN_OK;
-    k_pack_rgba8<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<uchar4*>(d_rgba), d_depth, npix);
+    k_pack_rgba8<<<cdiv64(npix, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_sum), reinterpret_cast<const float2*>(d_aux),
+                                                           reinterpret_cast<uchar4*>(d_rgba), d_depth, npix);
     VMN_CUDA(c, cudaGetLastError());
+    return VMN_OK;
+}
+
+// this context's share of the frame: interleaved tiles or a contiguous pixel range
+static vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* out, uint64_t* n_local_total) {
+    const uint64_t npix = c->film_pixels;
+    PixelMap pm{};
+    pm.width = c->cam.width; pm.height = c->cam.height;
+    if (prm->tile_size) {
+        if (!prm->tile_world || prm->tile_rank >= prm->tile_world) return fail(c, VMN_ERR_INVALID, "bad tile rank/world");
+        pm.tile = prm->tile_size; pm.rank = prm->tile_rank; pm.world = prm->tile_world;
+        pm.tiles_x = (pm.width + pm.tile - 1) / pm.tile;
+        const uint64_t tiles = (uint64_t)pm.tiles_x * ((pm.height + pm.tile - 1) / pm.tile);
+        const uint64_t mine = tiles > pm.rank ? (tiles - pm.rank + pm.world - 1) / pm.world : 0;
+        *n_local_total = mine * pm.tile * pm.tile;
+    } else {
+        const uint64_t pe = prm->pixel_end ? prm->pixel_end : npix;
+        if (prm->pixel_begin > pe || pe > npix) return fail(c, VMN_ERR_INVALID, "bad pixel range");
+        pm.begin = prm->pixel_begin;
+        *n_local_total = pe - prm->pixel_begin;
+    }
+    *out = pm;
     return VMN_OK;
 }
 
@@ -532,21 +601,9 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     const uint64_t npix = c->film_pixels;
     const uint32_t spp = c->cam.spp;
     PixelMap pm{};
-    pm.width = c->cam.width; pm.height = c->cam.height;
     uint64_t n_local_total;
-    if (prm->tile_size) {
-        if (!prm->tile_world || prm->tile_rank >= prm->tile_world) return fail(c, VMN_ERR_INVALID, "bad tile rank/world");
-        pm.tile = prm->tile_size; pm.rank = prm->tile_rank; pm.world = prm->tile_world;
-        pm.tiles_x = (pm.width + pm.tile - 1) / pm.tile;
-        const uint64_t tiles = (uint64_t)pm.tiles_x * ((pm.height + pm.tile - 1) / pm.tile);
-        const uint64_t mine = tiles > pm.rank ? (tiles - pm.rank + pm.world - 1) / pm.world : 0;
-        n_local_total = mine * pm.tile * pm.tile;
-    } else {
-        const uint64_t pe = prm->pixel_end ? prm->pixel_end : npix;
-        if (prm->pixel_begin > pe || pe > npix) return fail(c, VMN_ERR_INVALID, "bad pixel range");
-        pm.begin = prm->pixel_begin;
-        n_local_total = pe - prm->pixel_begin;
-    }
+    vmn_status s = make_pixel_map(c, prm, &pm, &n_local_total);
+    if (s != VMN_OK) return s;
     const int mode = prm->mode;
     uint32_t s_begin = 0, s_end = spp;
     if (mode == VMN_MODE_FIXED) {
@@ -567,8 +624,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
         if (batch > s_end - s_begin) batch = s_end - s_begin;
         if (batch < 1) batch = 1;
     }
-    vmn_status s = pool_ensure(c, chunk * batch);
-    if (s != VMN_OK) return s;
+    if ((s = pool_ensure(c, chunk * batch)) != VMN_OK) return s;
     PathPool* p = c->pool;
     if (mode == VMN_MODE_COMPAT && (s = dev_reserve(c, p->cstate, 4 * chunk)) != VMN_OK) return s;
     p->ev_used = 0;
@@ -642,6 +698,270 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 ++c->stats.kernel_launches;
                 c->stats.paths_traced += rp.n_local * rp.batch;
             }
+        }
+    }
+    VMN_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    VMN_CUDA(c, cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]);
+    c->stats.total_ms = ms;
+    double st[4] = {0, 0, 0, 0};
+    clk.collect(st);
+    c->stats.raygen_ms = st[ST_RAYGEN]; c->stats.extend_ms = st[ST_EXTEND]; c->stats.shade_ms = st[ST_SHADE]; c->stats.resolve_ms = st[ST_RESOLVE];
+    unsigned long long h[3] = {0, 0, 0};
+    VMN_CUDA(c, cudaMemcpy(h, p->ctl.as<char>() + kOffFrame, 24, cudaMemcpyDeviceToHost));
+    c->stats.nodes_visited = h[0]; c->stats.tris_tested = h[1]; c->stats.rays_traced = h[2];
+    return VMN_OK;
+}
+
+// ---- BruteForceTracer::Render (integrators.cpp:9-186) ---------------------------------------------------------------------------
+// The RenderEngine's default integrator (renderEngine.cpp:51) on the same wavefront: every live pixel takes one sample per round
+//   k_bf_raygen  jittered primary ray (integrators.cpp:65-81)                      -> queue 0, slot = local pixel
+//   k_extend     closest hit
+//   k_bf_shade1  RayCast finish, point-light N.L, normal-map perturbation (:83-106); a miss finishes the sample here;
+//                a hit emits the mirror-direction probe (:119-121) and, with VMN_RENDER_BF_SHADOW, the shadow ray -> queue 1
+//   k_extend     closest hit of the probes (and shadow rays: the any-hit helper RayCastCollision is a closest hit with t > 1e-3)
+//   k_bf_shade2  shadow (:108-110), probe miss lightening (:133-137), colour (:141-156), running mean and early-out (:158-173);
+//                a pixel that stops writes its film entry (:176-183)
+// RNG: Philox stream (seed, pixel, sample), draws 0 and 1 (the reference races one std::mt19937(time(0)) across threads, :30).
+struct BfParams {
+    uint64_t seed, n_local, lp0;
+    uint32_t sample, spp, flags;
+};
+
+// integrators.cpp:65-81
+__device__ __forceinline__ void bf_camera_ray(const CamDev& c, uint64_t p, float jx, float jy, V3* o, V3* d) {
+    float hx = (float)((((double)(float(p % c.width) + jx) - 0.25) / (double)c.width) * 2 - 1);
+    float hy = (float)((((double)(float(p / c.width) + jy) - 0.25) / (double)c.height) * 2 - 1);
+    float bx = (float)((double)(hx * c.sx) * 0.5), by = (float)((double)(hy * c.sy) * 0.5);
+    float g0 = bx, g1 = -by, g2 = -c.dist, g3 = 1.0f;
+    float rd[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) rd[r] = (c.m[r] * g0 + c.m[4 + r] * g1) + (c.m[8 + r] * g2 + c.m[12 + r] * g3);
+    V3 dir(rd[0] / rd[3], rd[1] / rd[3], rd[2] / rd[3]);
+    *d = normalize(dir);
+    *o = V3(c.px, c.py, c.pz);
+}
+
+__global__ void __launch_bounds__(kWfBlock) k_bf_raygen(CamDev cam, PixelMap pm, BfParams bp, const uint2* __restrict__ meta, float4* __restrict__ rays,
+                                                        uint32_t* __restrict__ qcount) {
+    const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool live = lp < bp.n_local;
+    uint64_t pixel = 0;
+    if (live) live = map_pixel(pm, bp.lp0 + lp, &pixel) && (meta[lp].y & 1u) == 0u;
+    V3 o(0, 0, 0), d(0, 0, 0);
+    if (live) {
+        Rng rng(bp.seed, pixel, bp.sample, 0);
+        const float jx = rng.jitter(), jy = rng.jitter();
+        bf_camera_ray(cam, pixel, jx, jy, &o, &d);
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, live);
+    if (ballot == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t base = 0;
+    if (lane == (uint32_t)(__ffs(ballot) - 1)) base = atomicAdd(qcount, (uint32_t)__popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
+    if (live) {
+        const uint32_t q = base + __popc(ballot & ((1u << lane) - 1u));
+        rays[2ull * q] = make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)lp));
+        rays[2ull * q + 1] = make_float4(d.x, d.y, d.z, 0.f);
+    }
+}
+
+// integrators.cpp:170: `abs` resolves to ::abs(int) in that translation unit, so the float sum is truncated to int first (x86
+// cvttss2si: INT_MIN for NaN / out of range; abs(INT_MIN) stays INT_MIN)
+__device__ __forceinline__ float abs_via_int(float x) {
+    const int i = (fabsf(x) < 2147483648.f) ? __float2int_rz(x) : (int)0x80000000;
+    const uint32_t a = i < 0 ? 0u - (uint32_t)i : (uint32_t)i;
+    return (float)(int)a;
+}
+
+// the end of one sample of pixel `lp` (integrators.cpp:141-173) and, when the pixel stops, its film entry (:176-183)
+__device__ __forceinline__ void bf_finish_sample(const SceneDev& sc, const PixelMap& pm, const BfParams& bp, uint32_t lp, bool hit, float vNDL, float u,
+                                                 float v, float dist, float4* __restrict__ accum_a, float4* __restrict__ last_a,
+                                                 uint2* __restrict__ meta_a, float4* __restrict__ film, float2* __restrict__ aux) {
+    float4 accum = accum_a[lp], last = last_a[lp];
+    const uint32_t n = meta_a[lp].x + 1u; // ++nTotalSamples (:63)
+    if (hit) {
+        float4 cur;
+        if (sc.tex1) { // :141-147
+            float c4[4];
+            texture_sample(sc.tex1, sc.tex1_w, sc.tex1_h, sc.tex1_c, u, v, c4);
+            cur = make_float4(c4[0] * vNDL, c4[1] * vNDL, c4[2] * vNDL, 1.0f);
+        } else {
+            cur = make_float4(0.890196078f * vNDL, 0.258823529f * vNDL, 0.203921569f * vNDL, 1.0f); // :150-155
+        }
+        accum.x += cur.x; accum.y += cur.y; accum.z += cur.z; accum.w += cur.w; // :158
+    }
+    const float fn = (float)n;
+    bool done = false;
+    if (n > 2u) { // :167-172
+        last.x -= accum.x / fn; last.y -= accum.y / fn; last.z -= accum.z / fn; last.w -= accum.w / fn;
+        if (abs_via_int(last.x + last.y + last.z + last.w) < 0.001f) done = true;
+    }
+    if (!done) last = make_float4(accum.x / fn, accum.y / fn, accum.z / fn, accum.w / fn); // :173
+    if (n >= bp.spp) done = true;
+    accum_a[lp] = accum; last_a[lp] = last; meta_a[lp] = make_uint2(n, done ? 1u : 0u);
+    if (done) {
+        uint64_t pixel;
+        if (map_pixel(pm, bp.lp0 + lp, &pixel)) {
+            film[pixel] = make_float4(accum.x, accum.y, accum.z, fn);
+            aux[pixel] = make_float2(accum.w, dist);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kWfBlock) k_bf_shade1(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, BfParams bp,
+                                                        const float4* __restrict__ rays, const float2* __restrict__ hits,
+                                                        const uint32_t* __restrict__ qcount_in, float4* __restrict__ rays_out,
+                                                        uint32_t* __restrict__ qcount_out, float4* __restrict__ accum, float4* __restrict__ last,
+                                                        uint2* __restrict__ meta, float4* __restrict__ tmp, float4* __restrict__ film,
+                                                        float2* __restrict__ aux) {
+    const uint32_t n = *qcount_in;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = (bp.flags & VMN_RENDER_BF_SHADOW) ? 2u : 1u;
+    for (uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; base < n; base += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = base + lane;
+        bool emit = false;
+        V3 P(0, 0, 0), sdir(0, 0, 0), ldir(0, 0, 0);
+        uint32_t slot = 0;
+        if (i < n) {
+            const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
+            const float2 hr = __ldg(&hits[i]);
+            slot = __float_as_uint(ra.w);
+            const V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
+            const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y)); // :81
+            if (!h.hit) {
+                bf_finish_sample(sc, pm, bp, slot, false, 0.f, 0.f, 0.f, h.dist, accum, last, meta, film, aux); // :160-164
+            } else {
+                const V3 lightLocation(500.f, 1100.f, 2000.f); // :16
+                ldir = normalize(lightLocation - h.P); // :83-84
+                V3 hn = h.N;
+                float vNDL = dot(ldir, normalize(hn)); // :88
+                if (sc.tex) { // :98-106
+                    float n4[4];
+                    texture_sample(sc, h.uv0, h.uv1, n4);
+                    hn = hn + V3(n4[0], n4[1], n4[2]);
+                    vNDL = dot(ldir, normalize(hn));
+                }
+                const V3 nl = -ldir;
+                sdir = nl - (hn * 2.f) * dot(hn, nl); // :119
+                P = h.P;
+                tmp[slot] = make_float4(vNDL, h.uv0, h.uv1, h.dist);
+                emit = true;
+            }
+        }
+        const uint32_t ballot = __ballot_sync(0xffffffffu, emit);
+        if (ballot) {
+            const int leader = __ffs(ballot) - 1;
+            uint32_t qb = 0;
+            if ((int)lane == leader) qb = atomicAdd(qcount_out, stride * (uint32_t)__popc(ballot));
+            qb = __shfl_sync(0xffffffffu, qb, leader);
+            if (emit) {
+                const uint64_t q = qb + stride * __popc(ballot & ((1u << lane) - 1u));
+                rays_out[2 * q] = make_float4(P.x, P.y, P.z, __uint_as_float(slot));
+                rays_out[2 * q + 1] = make_float4(sdir.x, sdir.y, sdir.z, 0.f);
+                if (stride == 2u) { // the shadow ray sits right behind its probe
+                    rays_out[2 * q + 2] = make_float4(P.x, P.y, P.z, __uint_as_float(slot));
+                    rays_out[2 * q + 3] = make_float4(ldir.x, ldir.y, ldir.z, 0.f);
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kWfBlock) k_bf_shade2(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, BfParams bp,
+                                                        const float4* __restrict__ rays, const float2* __restrict__ hits,
+                                                        const uint32_t* __restrict__ qcount_in, float4* __restrict__ accum, float4* __restrict__ last,
+                                                        uint2* __restrict__ meta, const float4* __restrict__ tmp, float4* __restrict__ film,
+                                                        float2* __restrict__ aux) {
+    const uint32_t stride = (bp.flags & VMN_RENDER_BF_SHADOW) ? 2u : 1u;
+    const uint32_t n = *qcount_in / stride;
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = (uint64_t)stride * j;
+        const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
+        const float2 hr = __ldg(&hits[i]);
+        const uint32_t slot = __float_as_uint(ra.w);
+        const RayCastOut h2 = raycast_finish(sc, sph, V3(ra.x, ra.y, ra.z), V3(rb.x, rb.y, rb.z), hr.x, __float_as_uint(hr.y)); // :121
+        const float4 t4 = tmp[slot];
+        float vNDL = t4.x;
+        if (stride == 2u) { // :108-110 with RayCastCollision's test (meshEngine.cpp:196-207)
+            const float2 hs = __ldg(&hits[i + 1]);
+            if (__float_as_uint(hs.y) != VMN_MISS && (double)hs.x > 1e-3) vNDL *= 0.00f;
+        }
+        if (!h2.hit) { vNDL *= 0.9f; vNDL += 0.1f; } // :133-137
+        bf_finish_sample(sc, pm, bp, slot, true, vNDL, t4.y, t4.z, t4.w, accum, last, meta, film, aux);
+    }
+}
+
+vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
+    const uint64_t npix = c->film_pixels;
+    const uint32_t spp = c->cam.spp;
+    if (spp > 65535u) return fail(c, VMN_ERR_INVALID, "BRUTEFORCE: spp %u > 65535 (the reference's uint16_t sample loop never ends, integrators.cpp:59)", spp);
+    if (prm->flags & VMN_RENDER_ACCUMULATE) return fail(c, VMN_ERR_INVALID, "VMN_RENDER_ACCUMULATE needs VMN_MODE_FIXED");
+    PixelMap pm{};
+    uint64_t n_local_total;
+    vmn_status s = make_pixel_map(c, prm, &pm, &n_local_total);
+    if (s != VMN_OK) return s;
+    c->stats.kernel_launches = 0; c->stats.rays_traced = 0; c->stats.paths_traced = 0;
+    c->stats.raygen_ms = c->stats.extend_ms = c->stats.shade_ms = c->stats.resolve_ms = c->stats.total_ms = 0;
+    if ((s = dev_reserve(c, c->film_aux, 8 * npix)) != VMN_OK) return s;
+    VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
+    VMN_CUDA(c, cudaMemsetAsync(c->film_aux.p, 0, 8 * npix, c->stream));
+    c->film_bf = true;
+    if (n_local_total == 0 || spp == 0) return VMN_OK; // spp == 0: the reference divides 0 by 0; here the film stays empty
+
+    const uint32_t stride = (prm->flags & VMN_RENDER_BF_SHADOW) ? 2u : 1u;
+    uint64_t chunk = c->max_paths / stride;
+    if (chunk > n_local_total) chunk = n_local_total;
+    if (chunk * stride >= 0xFFFFFFFFull) chunk = 0xFFFFFFF0ull / stride;
+    if ((s = pool_ensure(c, chunk * stride)) != VMN_OK) return s;
+    PathPool* p = c->pool;
+    if ((s = dev_reserve(c, p->bf_last, 16 * chunk)) != VMN_OK) return s;
+    p->ev_used = 0;
+    StageClock clk{c, p, {}};
+    uint32_t* qc = p->ctl.as<uint32_t>();
+    const CamDev cd = cam_dev(c);
+    const int grid = extend_grid(c, (c->flags & VMN_CFG_COUNTERS) != 0);
+    const SphereDev* sph = c->spheres.as<SphereDev>();
+    VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + kOffFrame, 0, 32, c->stream));
+
+    VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+    for (uint64_t lp0 = 0; lp0 < n_local_total; lp0 += chunk) {
+        BfParams bp{};
+        bp.seed = prm->seed; bp.lp0 = lp0; bp.n_local = (n_local_total - lp0 < chunk) ? n_local_total - lp0 : chunk;
+        bp.spp = spp; bp.flags = prm->flags;
+        VMN_CUDA(c, cudaMemsetAsync(p->radiance.p, 0, 16 * bp.n_local, c->stream)); // accum
+        VMN_CUDA(c, cudaMemsetAsync(p->bf_last.p, 0, 16 * bp.n_local, c->stream));  // lastSampleColour
+        VMN_CUDA(c, cudaMemsetAsync(p->meta.p, 0, 8 * bp.n_local, c->stream));      // (nTotalSamples, done)
+        for (uint32_t sample = 0; sample < spp; ++sample) {
+            bp.sample = sample;
+            VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 16, c->stream)); // queue counts + the two claim counters used below
+            clk.begin(ST_RAYGEN);
+            k_bf_raygen<<<cdiv64(bp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, bp, p->meta.as<uint2>(), p->ray[0].as<float4>(), qc);
+            clk.end();
+            ++c->stats.kernel_launches;
+            VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
+            VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+            const uint64_t live = p->h_count[0];
+            if (live == 0) break;
+            c->stats.paths_traced += live;
+            if ((s = launch_extend(c, p, 0, 0, &clk, grid)) != VMN_OK) return s;
+            clk.begin(ST_SHADE);
+            k_bf_shade1<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, sph, pm, bp, p->ray[0].as<float4>(), p->hit.as<float2>(), qc,
+                                                                     p->ray[1].as<float4>(), qc + 1, p->radiance.as<float4>(), p->bf_last.as<float4>(),
+                                                                     p->meta.as<uint2>(), p->thr.as<float4>(), c->film.as<float4>(),
+                                                                     c->film_aux.as<float2>());
+            clk.end();
+            if ((s = launch_extend(c, p, 1, 1, &clk, grid)) != VMN_OK) return s;
+            clk.begin(ST_SHADE);
+            k_bf_shade2<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, sph, pm, bp, p->ray[1].as<float4>(), p->hit.as<float2>(), qc + 1,
+                                                                     p->radiance.as<float4>(), p->bf_last.as<float4>(), p->meta.as<uint2>(),
+                                                                     p->thr.as<float4>(), c->film.as<float4>(), c->film_aux.as<float2>());
+            clk.end();
+            VMN_CUDA(c, cudaGetLastError());
+            c->stats.kernel_launches += 2;
         }
     }
     VMN_CUDA(c, cudaEventRecord(c->ev[5], c->stream));

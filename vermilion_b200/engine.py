@@ -19,10 +19,11 @@ RAYCAST = np.dtype([("P", "<f4", 3), ("dist", "<f4"), ("N", "<f4", 3), ("flags",
 SPHERE = np.dtype([("center", "<f4", 3), ("radius", "<f4"), ("emission", "<f4", 3), ("flags", "<u4"),
                    ("normal_center", "<f4", 3), ("pad", "<f4")])
 MISS = 0xFFFFFFFF
-MODE_COMPAT, MODE_FIXED = 0, 1
+MODE_COMPAT, MODE_FIXED, MODE_BRUTEFORCE = 0, 1, 2
 FILM_RGBAZ, FILM_SUM = 0, 1
 CFG_COUNTERS = 1
 RENDER_ACCUMULATE = 1
+RENDER_BF_SHADOW = 2
 ISECT_BVH2 = 1
 STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE"}
 
@@ -30,7 +31,7 @@ EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vm
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
            "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
-           "vmn_film_resolve_device", "vmn_read_image_rgba8", "vmn_get_stats"]
+           "vmn_film_resolve_device", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats"]
 
 
 class Config(C.Structure):
@@ -116,6 +117,7 @@ def load_library():
     L.vmn_read_image.argtypes = [vp, vp, i32]
     L.vmn_film_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_film_resolve_device.argtypes = [vp, vp, vp]
+    L.vmn_film_aux_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_read_image_rgba8.argtypes = [vp, vp, vp]
     L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
     _LIB = L
@@ -165,7 +167,16 @@ class Engine:
         self.close()
 
     # scene ------------------------------------------------------------------------------------------
-    def set_scene(self, pos, nrm=None, uv=None, spheres=None, texture=None):
+    def set_texture(self, slot, texture):
+        """MeshEngine::boundTextures[slot] (slot 0 or 1); texture: float32 [h, w, c] or None to unbind."""
+        if texture is None:
+            self._chk(self.L.vmn_scene_set_texture(self.h, slot, None, 0, 0, 0), "vmn_scene_set_texture")
+            return
+        tex = np.ascontiguousarray(texture, np.float32)
+        h, w, c = tex.shape
+        self._chk(self.L.vmn_scene_set_texture(self.h, slot, _p(tex), w, h, c), "vmn_scene_set_texture")
+
+    def set_scene(self, pos, nrm=None, uv=None, spheres=None, texture=None, texture1=None):
         """spheres: None = the reference's eight (meshEngine.cpp:377-500); an empty array disables them."""
         pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 9)
         nrm = None if nrm is None else np.ascontiguousarray(nrm, np.float32).reshape(-1, 9)
@@ -174,9 +185,9 @@ class Engine:
         sp = reference_spheres() if spheres is None else np.ascontiguousarray(spheres, SPHERE)
         self._chk(self.L.vmn_scene_set_spheres(self.h, _p(sp) if len(sp) else None, len(sp)), "vmn_scene_set_spheres")
         if texture is not None:
-            tex = np.ascontiguousarray(texture, np.float32)
-            h, w, c = tex.shape
-            self._chk(self.L.vmn_scene_set_texture(self.h, 0, _p(tex), w, h, c), "vmn_scene_set_texture")
+            self.set_texture(0, texture)
+        if texture1 is not None:
+            self.set_texture(1, texture1)
         self._chk(self.L.vmn_scene_commit(self.h), "vmn_scene_commit")
 
     # ray queries ------------------------------------------------------------------------------------
@@ -224,9 +235,9 @@ class Engine:
         return out
 
     def render(self, mode=MODE_FIXED, seed=1, max_segments=5, pixel_begin=0, pixel_end=0, sample_begin=0, sample_end=0, tile_size=0,
-               tile_rank=0, tile_world=1, accumulate=False):
+               tile_rank=0, tile_world=1, accumulate=False, shadow=False):
         prm = RenderParams(mode, max_segments, seed, pixel_begin, pixel_end, sample_begin, sample_end, tile_size, tile_rank, tile_world,
-                           RENDER_ACCUMULATE if accumulate else 0)
+                           (RENDER_ACCUMULATE if accumulate else 0) | (RENDER_BF_SHADOW if shadow else 0))
         self._chk(self.L.vmn_render(self.h, C.byref(prm)), "vmn_render")
 
     def read_image(self, layout=FILM_RGBAZ, out=None):
@@ -250,6 +261,11 @@ class Engine:
     def film_device(self):
         ptr, n = C.c_void_p(), C.c_uint64()
         self._chk(self.L.vmn_film_device(self.h, C.byref(ptr), C.byref(n)), "vmn_film_device")
+        return ptr.value, n.value
+
+    def film_aux_device(self):
+        ptr, n = C.c_void_p(), C.c_uint64()
+        self._chk(self.L.vmn_film_aux_device(self.h, C.byref(ptr), C.byref(n)), "vmn_film_aux_device")
         return ptr.value, n.value
 
     def resolve_device(self, d_sum_ptr, out=None):
