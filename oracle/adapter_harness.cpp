@@ -40,7 +40,10 @@ extern "C" int adapter_render(ref_scene* scene, const ref_camera_settings* s, in
 
     Vermilion::B200Options opt;
     opt.mode = mode; opt.seed = seed; opt.maxSegments = max_segments;
-    Vermilion::B200PathTracer* b200 = new Vermilion::B200PathTracer(opt);
+    // mode 2 = VMN_MODE_BRUTEFORCE selects the BruteForceTracer drop-in; bit 8 of `mode` turns its shadow rays on
+    opt.shadowRays = (mode & 0x100) != 0;
+    opt.mode = mode & 0xFF;
+    Vermilion::B200PathTracer* b200 = opt.mode == VMN_MODE_BRUTEFORCE ? new Vermilion::B200BruteForceTracer(opt) : new Vermilion::B200PathTracer(opt);
     Vermilion::Integrator* integrator = b200; // main.cpp:60-63
     integrator->Render(cams, static_cast<Vermilion::MeshEngine*>(ref_scene_mesh_engine(scene)));
     int rc = b200->ok() ? 0 : 1;

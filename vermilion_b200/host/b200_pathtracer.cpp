@@ -4,7 +4,8 @@
 //   geometry  : MeshEngine::sceneMeshes walked exactly as MeshEngine::createBVH does (core/engines/meshEngine.cpp:660-717),
 //               which defines the canonical triangle order; uv only when the mesh HasTextureCoords(0)
 //   spheres   : the eight analytic spheres hard-coded in MeshEngine::RayCast (meshEngine.cpp:377-500) via vmn_reference_spheres
-//   texture   : MeshEngine::boundTextures[0], the only one Radiance samples (pathtracer.cpp:62-80)
+//   texture   : MeshEngine::boundTextures[0], the only one Radiance samples (pathtracer.cpp:62-80), and boundTextures[1],
+//               BruteForceTracer's albedo (integrators.cpp:141-147)
 //   camera    : the public Camera fields the pixel loop reads (core/camera/camera.h:66-104)
 //   film      : written back into Camera::mImage in the layout of Camera::renderMode (camera.cpp:88-124)
 #include "b200_pathtracer.h"
@@ -76,10 +77,14 @@ bool B200PathTracer::uploadScene(MeshEngine* mEng)
     vmn_sphere spheres[8];
     vmn_reference_spheres(spheres);
     if ((mLastStatus = vmn_scene_set_spheres(mCtx, spheres, 8)) != VMN_OK) return fail("vmn_scene_set_spheres");
-    if (!mEng->boundTextures.empty())
+    for (uint32_t slot = 0; slot < 2; ++slot)
     {
-        const VermiTexture& t = mEng->boundTextures[0];
-        if ((mLastStatus = vmn_scene_set_texture(mCtx, 0, t.pData, t.nWidth, t.nHeight, t.nChannels)) != VMN_OK) return fail("vmn_scene_set_texture");
+        if (slot < mEng->boundTextures.size())
+        {
+            const VermiTexture& t = mEng->boundTextures[slot];
+            if ((mLastStatus = vmn_scene_set_texture(mCtx, slot, t.pData, t.nWidth, t.nHeight, t.nChannels)) != VMN_OK) return fail("vmn_scene_set_texture");
+        }
+        else vmn_scene_set_texture(mCtx, slot, nullptr, 0, 0, 0); // unbind
     }
     if ((mLastStatus = vmn_scene_commit(mCtx)) != VMN_OK) return fail("vmn_scene_commit");
     mSceneKey = mEng; mSceneFaces = nFaces; mSceneTextures = mEng->boundTextures.size();
@@ -106,6 +111,7 @@ void B200PathTracer::Render(std::vector<Vermilion::Camera*>& cameraList, MeshEng
         rp.mode = mOpt.mode; rp.max_segments = mOpt.maxSegments; rp.seed = mOpt.seed;
         rp.tile_size = mOpt.tileSize; rp.tile_rank = mOpt.tileRank; rp.tile_world = mOpt.tileWorld;
         rp.sample_begin = mOpt.sampleBegin; rp.sample_end = mOpt.sampleEnd;
+        if (mOpt.mode == VMN_MODE_BRUTEFORCE && mOpt.shadowRays) rp.flags |= VMN_RENDER_BF_SHADOW;
         if ((mLastStatus = vmn_render(mCtx, &rp)) != VMN_OK) { fail("vmn_render"); return; }
         vmn_get_stats(mCtx, &mStats);
 

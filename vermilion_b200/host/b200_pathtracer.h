@@ -7,6 +7,9 @@
 //     ...
 //     rEng->draw();                                                          // -> integrator->Render(mCameras, mMeshEngine)
 //
+// and Vermilion::B200BruteForceTracer for `new BruteForceTracer()`, the RenderEngine's default integrator
+// (renderEngine.cpp:51, core/integrators/integrators.cpp:9-186).
+//
 // It is compiled against the reference's own headers (core/integrators/integrators.h, core/camera/camera.h,
 // core/engines/meshEngine.h) and links only the C ABI in include/vermilion_b200.h — no CUDA headers, no CPU fallback:
 // when the GPU engine cannot be created Render() logs the error and leaves the film untouched (the reference's
@@ -26,7 +29,9 @@ namespace Vermilion
     struct B200Options
     {
         int device = 0;
-        int mode = VMN_MODE_COMPAT;      // the reference estimator; VMN_MODE_FIXED = exact spp, r2 = xi, <= maxSegments rays per path
+        int mode = VMN_MODE_COMPAT;      // the reference estimator; VMN_MODE_FIXED = exact spp, r2 = xi, <= maxSegments rays per path;
+                                         // VMN_MODE_BRUTEFORCE = BruteForceTracer::Render (what B200BruteForceTracer sets)
+        bool shadowRays = false;         // BRUTEFORCE: enable the shadow test the reference has commented out (integrators.cpp:108-110)
         uint32_t maxSegments = 5;
         uint64_t seed = 1;               // the reference seeds from std::random_device (pathtracer.cpp:231); here it is explicit
         uint64_t maxPathsInFlight = 0;   // 0 = library default
@@ -60,6 +65,14 @@ namespace Vermilion
         const void* mSceneKey = nullptr;
         uint64_t mSceneFaces = 0;
         size_t mSceneTextures = 0;
+    };
+
+    // Drop-in for `new BruteForceTracer()` (integrators.h:18-21): same adapter, VMN_MODE_BRUTEFORCE. boundTextures[0] is the
+    // normal map and boundTextures[1] the albedo, as in integrators.cpp:98-106 / :141-147.
+    class B200BruteForceTracer : public B200PathTracer
+    {
+    public:
+        explicit B200BruteForceTracer(B200Options options = B200Options()) : B200PathTracer((options.mode = VMN_MODE_BRUTEFORCE, options)) {}
     };
 }
 #endif
