@@ -183,6 +183,11 @@ vmn_status vmn_film_device(vmn_ctx* ctx, float** d_sum, uint64_t* n_floats);
 /* resolve an (externally reduced) sum buffer already on the device into RGBAZ on the host */
 vmn_status vmn_film_resolve_device(vmn_ctx* ctx, const float* d_sum, float* dst_rgbaz);
 
+/* restores the raw sum buffer (VMN_FILM_SUM layout, width*height*4 floats) from the host, e.g. from a checkpoint written by
+ * vermilion_b200/host/film_io.h, so that a progressive FIXED-mode render resumes with VMN_RENDER_ACCUMULATE at sample_begin =
+ * the checkpoint's sample count. (The reference has no checkpointing: its image lives only in Camera::mImage, main.cpp:94-95.) */
+vmn_status vmn_film_upload(vmn_ctx* ctx, const float* sum);
+
 /* BRUTEFORCE film: device pointer to the second accumulation plane, 2 floats per pixel (sum alpha, depth of the last primary
  * RayCast), which a multi-GPU host reduces together with vmn_film_device's plane (tiles sum with zeros). */
 vmn_status vmn_film_aux_device(vmn_ctx* ctx, float** d_aux, uint64_t* n_floats);

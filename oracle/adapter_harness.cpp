@@ -23,6 +23,10 @@ struct ref_camera_settings {
 };
 extern "C" void* ref_scene_mesh_engine(ref_scene*);
 
+static const char* g_checkpoint_path = nullptr;
+static uint32_t g_checkpoint_every = 0;
+extern "C" void adapter_set_checkpoint(const char* path, uint32_t every_spp) { g_checkpoint_path = path; g_checkpoint_every = every_spp; }
+
 extern "C" int adapter_render(ref_scene* scene, const ref_camera_settings* s, int render_mode, int mode, uint64_t seed, uint32_t max_segments,
                               float* image, uint64_t* rays_traced, char* err, int errlen) {
     Vermilion::cameraSettings vcs;
@@ -41,6 +45,7 @@ extern "C" int adapter_render(ref_scene* scene, const ref_camera_settings* s, in
     Vermilion::B200Options opt;
     opt.mode = mode; opt.seed = seed; opt.maxSegments = max_segments;
     // mode 2 = VMN_MODE_BRUTEFORCE selects the BruteForceTracer drop-in; bit 8 of `mode` turns its shadow rays on
+    if (g_checkpoint_path) { opt.checkpointPath = g_checkpoint_path; opt.checkpointEverySpp = g_checkpoint_every; }
     opt.shadowRays = (mode & 0x100) != 0;
     opt.mode = mode & 0xFF;
     Vermilion::B200PathTracer* b200 = opt.mode == VMN_MODE_BRUTEFORCE ? new Vermilion::B200BruteForceTracer(opt) : new Vermilion::B200PathTracer(opt);

@@ -91,3 +91,39 @@ def test_bruteforce_adapter_matches_oracle_through_the_integrator_interface(shad
     assert taken.max() > 3 and abs(nrays - nq) <= 0.01 * nq
     rc, rgba, _, err = adapter_render(ref, cs, RGBA, 2 | (0x100 if shadow else 0), 11)  # through Camera::setPixelValue
     assert rc == 0 and np.array_equal(rgba.view(np.uint32), img[:, :4].view(np.uint32))
+
+
+@pytest.mark.gpu
+@needs_adapter
+def test_adapter_progressive_checkpoints_resume(tmp_path):
+    """B200Options::checkpointPath: slices of 4 spp with a checkpoint after each; a run that finds the checkpoint of an interrupted
+    render (here: one cut down to its first 8 of 16 spp) finishes it, and both equal the one-shot frame bit for bit."""
+    from vermilion_b200 import film_io
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    ref = checker.Ref(pos, nrm, uv)
+    cs = checker.camera_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16)
+    rc, one_shot, _, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
+    assert rc == 0, err
+    L = C.CDLL(ADAPTER)
+    L.adapter_set_checkpoint.argtypes = [C.c_char_p, C.c_uint32]
+    path = str(tmp_path / "film.vmn").encode()
+    try:
+        L.adapter_set_checkpoint(path, 4)
+        rc, img, _, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
+        assert rc == 0, err
+        assert np.array_equal(img.view(np.uint32), one_shot.view(np.uint32))
+        film, hdr = film_io.checkpoint_load(path.decode())
+        assert hdr.spp_done == 16 and hdr.spp_total == 16 and hdr.seed == 11
+        # rebuild the state of a run interrupted after 8 spp and let the adapter resume it
+        from vermilion_b200 import engine
+        with engine.Engine(device=0) as eng:
+            eng.set_scene(pos, nrm, uv)
+            eng.set_camera(engine.camera_from_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16))
+            eng.render(mode=engine.MODE_FIXED, seed=11, sample_begin=0, sample_end=8)
+            film_io.checkpoint_save(path.decode(), eng.read_image(engine.FILM_SUM), 64, 48, 8, 16, 11)
+        rc, img, nrays, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
+        assert rc == 0, err
+        assert np.array_equal(img.view(np.uint32), one_shot.view(np.uint32))
+        assert film_io.checkpoint_info(path.decode()).spp_done == 16
+    finally:
+        L.adapter_set_checkpoint(None, 0)

@@ -386,6 +386,17 @@ vmn_status vmn_film_device(vmn_ctx* c, float** d_sum, uint64_t* n_floats) {
     return VMN_OK;
 }
 
+vmn_status vmn_film_upload(vmn_ctx* c, const float* sum) {
+    CHECK_CTX(c);
+    if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
+    if (!sum) return fail(c, VMN_ERR_INVALID, "null pointer");
+    SET_DEVICE(c);
+    VMN_CUDA(c, cudaMemcpyAsync(c->film.p, sum, 16 * c->film_pixels, cudaMemcpyHostToDevice, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // the host pointer is borrowed for the call only
+    c->film_bf = false;
+    return VMN_OK;
+}
+
 vmn_status vmn_film_aux_device(vmn_ctx* c, float** d_aux, uint64_t* n_floats) {
     CHECK_CTX(c);
     if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");

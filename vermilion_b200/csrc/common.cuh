@@ -139,6 +139,7 @@ struct Rng {
         ++draw;
         return lane == 0 ? cache[0] : lane == 1 ? cache[1] : lane == 2 ? cache[2] : cache[3];
     }
+    __device__ void skip(uint32_t n) { draw += n; } // draws the reference makes and never uses: advance the counter, generate nothing
     __device__ double next01() { return (double)next_u32() * (1.0 / 4294967296.0); }
     __device__ float jitter() { return (float)(next_u32() >> 8) * (1.0f / 16777216.0f) * 0.5f; }
 };

@@ -265,26 +265,30 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                     float sc4[4] = {1.f, 1.f, 1.f, 1.f};
                     if (h.material && sc.tex) texture_sample(sc, h.uv0, h.uv1, sc4); // :62-80
                     if (h.material && rng.next01() >= 0.96) { // mirror :98-109
-                        rng.next01(); rng.next01(); rng.next01();
+                        rng.skip(3);
                         nStart = h.P - rDir * 0.001f;
                         nDir = normalize(rDir - h.N * 2.f * dot(h.N, rDir));
-                    } else if (h.material) { // diffuse :151-165
-                        tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3];
-                        float r1 = (float)(2 * 3.14159265358979323846 * rng.next01());
-                        float r2 = (float)((double)r2scale * rng.next01());
-                        float r2s = sqrtf(r2);
+                    } else {
+                        // diffuse off a triangle (:151-165) or off a sphere (:166-190): the two branches differ in where the draws are narrowed
+                        // to float, and share one sincos + hemisphere frame (a warp almost always holds both kinds of hit)
+                        const double xi1 = rng.next01(), xi2 = rng.next01();
+                        double r1d;
+                        float r2s, sq;
+                        if (h.material) {
+                            tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3];
+                            const float r1 = (float)(2 * 3.14159265358979323846 * xi1);
+                            const float r2 = (float)((double)r2scale * xi2);
+                            r2s = sqrtf(r2); sq = sqrtf(1 - r2);
+                            r1d = (double)r1; // cos(r1), sin(r1) of pathtracer.cpp:160 take the float r1 promoted to double
+                        } else {
+                            r1d = 2 * 3.14159265358979323846 * xi1;
+                            const double r2 = (double)r2scale * xi2;
+                            r2s = (float)sqrt(r2); sq = (float)sqrt(1 - r2);
+                            rng.skip(3); // :172-174 draw three unused numbers
+                        }
                         double s1, c1;
-                        sincos((double)r1, &s1, &c1); // cos(r1), sin(r1) of pathtracer.cpp:160 (float r1 promoted to double)
-                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, sqrtf(1 - r2));
-                        nStart = h.P - rDir * 0.001f;
-                    } else { // sphere-only hit :166-190
-                        double r1 = 2 * 3.14159265358979323846 * rng.next01();
-                        double r2 = (double)r2scale * rng.next01();
-                        float r2s = (float)sqrt(r2);
-                        rng.next01(); rng.next01(); rng.next01();
-                        double s1, c1;
-                        sincos(r1, &s1, &c1);
-                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, (float)sqrt(1 - r2));
+                        sincos(r1d, &s1, &c1);
+                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, sq);
                         nStart = h.P - rDir * 0.001f;
                     }
                 }

@@ -31,7 +31,7 @@ EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vm
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
            "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
-           "vmn_film_resolve_device", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats"]
+           "vmn_film_resolve_device", "vmn_film_upload", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats"]
 
 
 class Config(C.Structure):
@@ -117,6 +117,7 @@ def load_library():
     L.vmn_read_image.argtypes = [vp, vp, i32]
     L.vmn_film_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_film_resolve_device.argtypes = [vp, vp, vp]
+    L.vmn_film_upload.argtypes = [vp, vp]
     L.vmn_film_aux_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_read_image_rgba8.argtypes = [vp, vp, vp]
     L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -262,6 +263,12 @@ class Engine:
         ptr, n = C.c_void_p(), C.c_uint64()
         self._chk(self.L.vmn_film_device(self.h, C.byref(ptr), C.byref(n)), "vmn_film_device")
         return ptr.value, n.value
+
+    def upload_film(self, film_sum):
+        """restore the raw sum film (FILM_SUM layout) — resume point of a progressive render"""
+        film_sum = np.ascontiguousarray(film_sum, np.float32)
+        assert film_sum.shape == (self.cam.width * self.cam.height, 4)
+        self._chk(self.L.vmn_film_upload(self.h, _p(film_sum)), "vmn_film_upload")
 
     def film_aux_device(self):
         ptr, n = C.c_void_p(), C.c_uint64()

@@ -9,6 +9,7 @@
 //   camera    : the public Camera fields the pixel loop reads (core/camera/camera.h:66-104)
 //   film      : written back into Camera::mImage in the layout of Camera::renderMode (camera.cpp:88-124)
 #include "b200_pathtracer.h"
+#include "film_io.h"
 
 #include <cstdio>
 #include <cstring>
@@ -91,6 +92,43 @@ bool B200PathTracer::uploadScene(MeshEngine* mEng)
     return true;
 }
 
+// FIXED mode in slices of checkpointEverySpp samples, the film sums saved after every slice; a checkpoint of the same frame
+// (size, spp, seed, segment cap) is picked up where it stopped. Slices accumulate in the per-pixel sample order, so the result is
+// bit-identical to the one-shot render.
+bool B200PathTracer::renderProgressive(const vmn_camera& vc)
+{
+    const uint64_t npix = (uint64_t)vc.width * vc.height;
+    std::vector<float> film(4 * npix);
+    uint32_t done = 0;
+    vmnh_checkpoint_header h{};
+    if (vmnh_checkpoint_info(mOpt.checkpointPath.c_str(), &h) == 0 && h.width == vc.width && h.height == vc.height && h.spp_total == vc.spp &&
+        h.seed == mOpt.seed && h.max_segments == mOpt.maxSegments && h.spp_done <= vc.spp &&
+        vmnh_checkpoint_load(mOpt.checkpointPath.c_str(), film.data(), film.size(), &h) == 0)
+    {
+        if ((mLastStatus = vmn_film_upload(mCtx, film.data())) != VMN_OK) return fail("vmn_film_upload");
+        done = h.spp_done;
+        fprintf(stderr, "[B200PathTracer] resuming %s at %u of %u spp\n", mOpt.checkpointPath.c_str(), done, vc.spp);
+    }
+    const uint32_t every = mOpt.checkpointEverySpp ? mOpt.checkpointEverySpp : vc.spp;
+    bool first = done == 0;
+    while (done < vc.spp)
+    {
+        vmn_render_params rp{};
+        rp.mode = VMN_MODE_FIXED; rp.max_segments = mOpt.maxSegments; rp.seed = mOpt.seed;
+        rp.sample_begin = done; rp.sample_end = done + every < vc.spp ? done + every : vc.spp;
+        rp.flags = first ? 0u : VMN_RENDER_ACCUMULATE;
+        if ((mLastStatus = vmn_render(mCtx, &rp)) != VMN_OK) return fail("vmn_render");
+        first = false;
+        done = rp.sample_end;
+        if ((mLastStatus = vmn_read_image(mCtx, film.data(), VMN_FILM_SUM)) != VMN_OK) return fail("vmn_read_image");
+        memcpy(h.magic, "VMNFILM1", 8);
+        h.width = vc.width; h.height = vc.height; h.spp_done = done; h.spp_total = vc.spp; h.seed = mOpt.seed; h.max_segments = mOpt.maxSegments;
+        if (vmnh_checkpoint_save(mOpt.checkpointPath.c_str(), film.data(), &h) != 0)
+            fprintf(stderr, "[B200PathTracer] cannot write checkpoint %s\n", mOpt.checkpointPath.c_str());
+    }
+    return true;
+}
+
 void B200PathTracer::Render(std::vector<Vermilion::Camera*>& cameraList, MeshEngine* mEng)
 {
     if (!mCtx) { fprintf(stderr, "[B200PathTracer] no GPU engine (there is no CPU fallback); frame not rendered\n"); return; }
@@ -112,7 +150,9 @@ void B200PathTracer::Render(std::vector<Vermilion::Camera*>& cameraList, MeshEng
         rp.tile_size = mOpt.tileSize; rp.tile_rank = mOpt.tileRank; rp.tile_world = mOpt.tileWorld;
         rp.sample_begin = mOpt.sampleBegin; rp.sample_end = mOpt.sampleEnd;
         if (mOpt.mode == VMN_MODE_BRUTEFORCE && mOpt.shadowRays) rp.flags |= VMN_RENDER_BF_SHADOW;
-        if ((mLastStatus = vmn_render(mCtx, &rp)) != VMN_OK) { fail("vmn_render"); return; }
+        const bool progressive = !mOpt.checkpointPath.empty() && mOpt.mode == VMN_MODE_FIXED && mOpt.tileSize == 0 && mOpt.sampleEnd == 0;
+        if (progressive) { if (!renderProgressive(vc)) return; }
+        else if ((mLastStatus = vmn_render(mCtx, &rp)) != VMN_OK) { fail("vmn_render"); return; }
         vmn_get_stats(mCtx, &mStats);
 
         const uint64_t npix = (uint64_t)vc.width * vc.height;

@@ -38,6 +38,10 @@ namespace Vermilion
         // multi-GPU share of the frame (one process per GPU; the caller all-reduces the film)
         uint32_t tileSize = 0, tileRank = 0, tileWorld = 1;
         uint32_t sampleBegin = 0, sampleEnd = 0;
+        // progressive rendering with checkpoints (FIXED mode, whole sample range): the film sums are written to checkpointPath
+        // (film_io.h) every checkpointEverySpp samples and a matching checkpoint found there is resumed instead of starting over
+        std::string checkpointPath;
+        uint32_t checkpointEverySpp = 0;
     };
 
     class B200PathTracer : public Integrator
@@ -54,6 +58,7 @@ namespace Vermilion
 
     private:
         bool uploadScene(MeshEngine* mEng);
+        bool renderProgressive(const vmn_camera& vc);
         bool fail(const char* what);
 
         B200Options mOpt;
