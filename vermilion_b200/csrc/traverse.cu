@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
                                                            vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt,
                                                            uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
-    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
+    __shared__ __align__(16) uint32_t wscratch_all[VMN_WSCRATCH * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
     auto finish = [&](uint64_t i, V3 o, V3 d, float t, uint32_t id) { // id: original triangle id or VMN_MISS
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
         reinterpret_cast<float4*>(out)[i] = make_float4(t, u, v, __uint_as_float(id));
     };
     if (WIDE) {
-        persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+        persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                                 [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
                                 [&](uint64_t i, const Trav& s) { finish(i, s.o, s.d, s.best_t, leaf_original_id(sc.tris, s.best)); });
     } else {
@@ -69,10 +69,10 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
 __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_occluded(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n, uint8_t* __restrict__ out,
                                                           unsigned long long* next, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
-    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
+    __shared__ __align__(16) uint32_t wscratch_all[VMN_WSCRATCH * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
-    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
                             [&](uint64_t i, const Trav& s) { out[i] = (s.best != VMN_MISS && (double)s.best_t > 1e-3) ? 1 : 0; }); // meshEngine.cpp:196-207
 }
@@ -80,10 +80,10 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_occluded(SceneD
 __global__ void __launch_bounds__(kTraceBlock, 6) k_raycast(SceneDev sc, const SphereDev* __restrict__ sph, const vmn_ray* __restrict__ rays, uint64_t n,
                                                          vmn_raycast_rec* __restrict__ out, unsigned long long* next, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
-    __shared__ uint32_t wscratch_all[64 * (kTraceBlock / 32)];
+    __shared__ __align__(16) uint32_t wscratch_all[VMN_WSCRATCH * (kTraceBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     TravCounters cnt{0ull, 0ull};
-    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+    persistent_trace<false>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) { load_ray(rays, i, o, d); },
                             [&](uint64_t i, const Trav& s) {
                                 const RayCastOut r = raycast_finish(sc, sph, s.o, s.d, s.best_t, leaf_original_id(sc.tris, s.best));

@@ -24,6 +24,10 @@ namespace vmn {
 #ifndef VMN_PREFETCH
 #define VMN_PREFETCH 0
 #endif
+#ifndef VMN_COOP_ATOMIC
+#define VMN_COOP_ATOMIC 1     // fold pooled triangle results with a shared 64-bit atomicMin per hit instead of a per-owner loop
+#endif
+#define VMN_WSCRATCH 96       // words of shared scratch per warp (trav_tris_coop)
 #ifndef VMN_COOP
 #define VMN_COOP 1            // warp-pooled triangle tests (trav_tris_coop); 0 = per-lane loop
 #endif
@@ -246,7 +250,7 @@ __device__ __forceinline__ bool trav_pop(Trav& s, const uint2* sstack, uint32_t 
 // threads). Here the warp's pending (ray, triangle) pairs are numbered by a prefix sum and dealt one per lane: lane j takes
 // pair j, fetches the owner's ray by shuffle, tests, and posts t to shared memory; each owner then folds its results in
 // triangle order with the reference's strict `<` (bvh.cpp:90), so the outcome is identical to the per-lane loop.
-// wscratch: 64 words of shared memory per warp. Must be called by all 32 lanes.
+// wscratch: VMN_WSCRATCH words of shared memory per warp. Must be called by all 32 lanes.
 template <bool COUNT>
 __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const SceneDev& sc, uint32_t* wscratch, TravCounters* cnt) {
     const uint32_t FULL = 0xffffffffu;
@@ -263,7 +267,16 @@ __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const Scene
     }
     const uint32_t excl = incl - n;
     uint32_t* w_owner = wscratch;
+#if VMN_COOP_ATOMIC
+    // results are folded with one 64-bit shared atomicMin per HIT on the owner's key (t bits << 32 | leaf index): positive floats order
+    // as their bit patterns, the smaller leaf index wins an exact tie among the pooled triangles (= triangle order), and the owner's
+    // current best enters with index 0 so that it wins ties against all of them — the strict `<` of bvh.cpp:90. wscratch: 96 words.
+    unsigned long long* w_key = reinterpret_cast<unsigned long long*>(wscratch + 32);
+    const unsigned long long key0 = (unsigned long long)__float_as_uint(s.best_t) << 32;
+    if (n) w_key[lane] = key0;
+#else
     float* w_res = reinterpret_cast<float*>(wscratch + 32);
+#endif
     for (uint32_t w0 = 0; w0 < total; w0 += 32u) { // warp-uniform; one trip unless more than 32 pairs are pending
         const bool has = n != 0u && excl < w0 + 32u && incl > w0;
         const uint32_t lo = excl > w0 ? excl : w0;          // first of my pairs inside the window
@@ -281,12 +294,19 @@ __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const Scene
         if (work) {
             uint32_t b = o_bits;
             for (uint32_t k = j - o_excl; k; --k) b &= b - 1u;
-            const TriRec T = load_tri(sc.tris + o_base + (__ffs(b) - 1u));
+            const uint32_t ti = o_base + (__ffs(b) - 1u);
+            const TriRec T = load_tri(sc.tris + ti);
             if (COUNT) ++cnt->tris;
             float ct;
+#if VMN_COOP_ATOMIC
+            if (tri_intersect(T, V3(ox, oy, oz), V3(dx, dy, dz), &ct))
+                atomicMin(&w_key[owner], ((unsigned long long)__float_as_uint(ct) << 32) | ti);
+#else
             w_res[lane] = tri_intersect(T, V3(ox, oy, oz), V3(dx, dy, dz), &ct) ? ct : INFINITY;
+#endif
         }
         __syncwarp();
+#if !VMN_COOP_ATOMIC
         if (has) {
             uint32_t b = bits;
             for (uint32_t k = lo - excl; k; --k) b &= b - 1u;
@@ -299,7 +319,14 @@ __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const Scene
             }
         }
         __syncwarp();
+#endif
     }
+#if VMN_COOP_ATOMIC
+    if (n) {
+        const unsigned long long k = w_key[lane];
+        if (k != key0) { s.best_t = __uint_as_float((uint32_t)(k >> 32)); s.best = (uint32_t)k; }
+    }
+#endif
     s.tg.y = 0u;
 }
 

@@ -169,12 +169,12 @@ __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev s
                                                      float2* __restrict__ hits, unsigned long long* next, TravCounters* gcnt,
                                                      unsigned long long* total_rays, uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
-    __shared__ uint32_t wscratch_all[64 * (kWfBlock / 32)];
+    __shared__ __align__(16) uint32_t wscratch_all[VMN_WSCRATCH * (kWfBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     const uint64_t n = *qcount;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total_rays, (unsigned long long)n);
     TravCounters cnt{0ull, 0ull};
-    persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, wscratch_all + 64 * (threadIdx.x >> 5), &cnt,
+    persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) {
                                 const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
                                 *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
