@@ -72,9 +72,13 @@ __device__ __forceinline__ bool ray_is_nan(V3 o, V3 d) {
     return !(o.x == o.x && o.y == o.y && o.z == o.z && d.x == d.x && d.y == d.y && d.z == d.z);
 }
 
+// 1 / d for the slab tests only (never for an output value): MUFU.RCP, 1 ulp. Both planes of an axis use the same reciprocal, so its error
+// moves an axis interval as a whole by a relative 2^-23 — the same size as the rounding of (p - o) * idx that the slab margins already absorb.
 __device__ __forceinline__ float safe_inv(float x) {
     const float eps = 1e-20f;
-    return 1.0f / (fabsf(x) > eps ? x : copysignf(eps, x));
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fabsf(x) > eps ? x : copysignf(eps, x)));
+    return r;
 }
 
 // ---- compressed BVH8 closest hit --------------------------------------------------------------
@@ -95,10 +99,14 @@ struct Trav {
 // distance q*a + b is then evaluated as fma(1 + q*2^-15, a*2^15, b - a*2^15): one PRMT + one FFMA per plane. (I2F.U8 runs on the
 // quarter-rate XU pipe and was 33 % of all stall samples in the first profile; the 2^23-bias form needed an extra FADD per plane.)
 // Rounding of b - a*2^15 costs at most 2^-9 of a quantisation cell; trav_node() widens every slab by 2^-8 cell to stay conservative.
+// `one` must be 0x3F800000 held in a REGISTER (see opaque_one): PRMT takes a single immediate, and with the constant known ptxas spends
+// it on 0x3F800000 and re-materialises the selector from a uniform register before every PRMT (one extra IMAD.U32 per plane, 48 per node).
 template <int J>
-__device__ __forceinline__ float byte_to_unit(uint32_t w) {
-    return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | (J << 4)));
+__device__ __forceinline__ float byte_to_unit(uint32_t w, uint32_t one) {
+    return __uint_as_float(__byte_perm(w, one, 0x7604u | (J << 4)));
 }
+// 0x3F800000 that the compiler cannot constant-fold (n_tris < 2^31 always)
+__device__ __forceinline__ uint32_t opaque_one(const SceneDev& sc) { return 0x3F800000u | (sc.n_tris >> 31); }
 
 __device__ __forceinline__ bool trav_init(Trav& s, const SceneDev& sc, V3 o, V3 d) {
     s.o = o; s.d = d;
@@ -115,13 +123,13 @@ __device__ __forceinline__ bool trav_init(Trav& s, const SceneDev& sc, V3 o, V3 
 template <int J>
 __device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint32_t nyw, uint32_t nzw, uint32_t fxw, uint32_t fyw, uint32_t fzw,
                                               float ax, float ay, float az, float nbx, float nby, float nbz, float fbx, float fby, float fbz,
-                                              float best_t, uint32_t oct_inv) {
-    const float tnx = __fmaf_rn(byte_to_unit<J>(nxw), ax, nbx);
-    const float tny = __fmaf_rn(byte_to_unit<J>(nyw), ay, nby);
-    const float tnz = __fmaf_rn(byte_to_unit<J>(nzw), az, nbz);
-    const float tfx = __fmaf_rn(byte_to_unit<J>(fxw), ax, fbx);
-    const float tfy = __fmaf_rn(byte_to_unit<J>(fyw), ay, fby);
-    const float tfz = __fmaf_rn(byte_to_unit<J>(fzw), az, fbz);
+                                              float best_t, uint32_t oct_inv, uint32_t one) {
+    const float tnx = __fmaf_rn(byte_to_unit<J>(nxw, one), ax, nbx);
+    const float tny = __fmaf_rn(byte_to_unit<J>(nyw, one), ay, nby);
+    const float tnz = __fmaf_rn(byte_to_unit<J>(nzw, one), az, nbz);
+    const float tfx = __fmaf_rn(byte_to_unit<J>(fxw, one), ax, fbx);
+    const float tfy = __fmaf_rn(byte_to_unit<J>(fyw, one), ay, fby);
+    const float tfz = __fmaf_rn(byte_to_unit<J>(fzw, one), az, fbz);
     const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
     const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
 #if VMN_HIT8
@@ -173,11 +181,12 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
         const uint32_t ny0 = ngy ? q4.x : q2.z, ny1 = ngy ? q4.y : q2.w, fy0 = ngy ? q2.z : q4.x, fy1 = ngy ? q2.w : q4.y;
         const uint32_t nz0 = ngz ? q4.z : q3.x, nz1 = ngz ? q4.w : q3.y, fz0 = ngz ? q3.x : q4.z, fz1 = ngz ? q3.y : q4.w;
         uint32_t hitmask = 0;
+        const uint32_t one = opaque_one(sc);
 #if VMN_HIT8
         // one hit bit per child slot, then a single expansion per node: internal hits are moved to the octant-ordered positions
         // 24 + (slot ^ oct_inv) by three conditional bit swaps; leaf hits OR in their unary triangle masks (usually 0-2 leaves)
         uint32_t hit8 = 0;
-#define VMN_CH(J, MW, S) hit8 |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv) << (4 * S + J)
+#define VMN_CH(J, MW, S) hit8 |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv, one) << (4 * S + J)
         VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
         VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
 #undef VMN_CH
@@ -197,7 +206,7 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             }
         }
 #else
-#define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv)
+#define VMN_CH(J, MW, S) hitmask |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv, one)
         VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
         VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
 #undef VMN_CH
