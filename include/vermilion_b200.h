@@ -161,7 +161,7 @@ vmn_status vmn_occluded(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, uint8_t* 
 /* replaces MeshEngine::RayCast (meshEngine.cpp:239-509) for n rays */
 vmn_status vmn_raycast(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, vmn_raycast_rec* out);
 /* replaces Radiance() (pathtracer.cpp:21-198) for n start rays: Philox stream (seed, pixel = i, sample 0),
- * draws start at index 2. out: 4 floats per ray; rays_cast (optional): RayCast count per path. */
+ * iteration i (1-based) of the bounce loop draws from Philox block i. out: 4 floats per ray; rays_cast (optional): RayCast count per path. */
 vmn_status vmn_radiance(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, uint64_t seed, int32_t mode, uint32_t max_segments,
                         float* out, uint32_t* rays_cast);
 

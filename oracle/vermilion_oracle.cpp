@@ -80,6 +80,9 @@ struct RngPhilox {
     uint32_t cached_block;
     RngPhilox(uint64_t s, uint64_t p) : seed(s), pixel(p), sample(0), draw(0), cached_block(0xFFFFFFFFu) {}
     void begin_sample(uint32_t s) { sample = s; draw = 0; cached_block = 0xFFFFFFFFu; }
+    // iteration i (1-based) of the bounce loop draws from Philox block i: at most four numbers are used per iteration (roulette, mirror
+    // test, two angles; the reference's three unused noise draws only advance the counter), so the GPU generates one block per bounce
+    void begin_bounce(uint32_t i) { draw = 4u * i; }
     uint32_t next_u32() {
         uint32_t block = draw >> 2, lane = draw & 3u;
         if (block != cached_block) {
@@ -101,6 +104,7 @@ struct RngMt64 {
     std::mt19937_64 eng;
     explicit RngMt64(uint64_t s) : eng(s) {}
     void begin_sample(uint32_t) {}
+    void begin_bounce(uint32_t) {}
     double next01() { std::uniform_real_distribution<double> d(0.0, 1.0); return d(eng); }
     float jitter() { std::uniform_real_distribution<float> d(0, 0.5); return d(eng); }
 };
@@ -413,6 +417,7 @@ inline V4 radiance(const orc_scene& sc, V3 rStart, V3 rDir, Rng& rng, int mode, 
     while (1) {
         RayCastOut h = ray_cast(sc, rStart, rDir);
         ++segs;
+        rng.begin_bounce(segs);
         if (nrays) ++*nrays;
         if (!h.hit) return accumColour; // :37-41
         accumColour.x += accumRadiance.x * h.Le.x; // :43

@@ -91,7 +91,7 @@ void orc_raycast_many(const orc_scene*, const orc_ray* rays, uint64_t n, orc_ray
 
 /* Radiance (pathtracer.cpp:21-198) for n start rays. rng_kind MT64: engine i is
  * std::mt19937_64(seed + i). PHILOX: stream (seed, pixel=i, sample=0), draws
- * start at index first_draw. mode FIXED = documented fixed estimator.
+ * of bounce-loop iteration i (1-based) come from Philox block i. mode FIXED = documented fixed estimator.
  * out: 4 floats per ray; rays_cast (optional): RayCast calls per ray. */
 void orc_radiance_many(const orc_scene*, const orc_ray* rays, uint64_t n, uint64_t seed, int rng_kind, int mode,
                        float* out, uint32_t* rays_cast, int threads);

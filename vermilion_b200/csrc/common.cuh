@@ -144,4 +144,20 @@ struct Rng {
     __device__ float jitter() { return (float)(next_u32() >> 8) * (1.0f / 16777216.0f) * 0.5f; }
 };
 
+// The four numbers of one bounce-loop iteration: Philox block `iteration` of stream (seed, pixel, sample), consumed in order.
+struct BounceRng {
+    uint32_t r[4];
+    uint32_t k;
+    __device__ void init(uint64_t seed, uint64_t pixel, uint32_t sample, uint32_t iteration) {
+        r[0] = (uint32_t)pixel; r[1] = (uint32_t)(pixel >> 32); r[2] = sample; r[3] = iteration;
+        philox4x32_10(r, (uint32_t)seed, (uint32_t)(seed >> 32));
+        k = 0;
+    }
+    __device__ double next01() {
+        const uint32_t v = k == 0 ? r[0] : k == 1 ? r[1] : k == 2 ? r[2] : r[3];
+        ++k;
+        return (double)v * (1.0 / 4294967296.0);
+    }
+};
+
 } // namespace vmn

@@ -252,20 +252,23 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                 uint64_t pixel; uint32_t sample;
                 if (radiance_query) { pixel = slot; sample = 0; }
                 else { map_pixel(pm, rp.lp0 + (slot % rp.n_local), &pixel); sample = rp.s0 + (uint32_t)(slot / rp.n_local); }
-                Rng rng(rp.seed, pixel, sample, mt.x);
+                // iteration `segs` of the path draws from Philox block `segs` (block 0 holds the two pixel jitters): one block per bounce,
+                // generated once by every lane that still needs numbers; at most four are used (roulette, mirror test, two angles)
+                BounceRng rng;
                 if (rp.mode == VMN_MODE_FIXED) {
                     ++depth;
                     if (segs >= rp.max_segments) alive = false;
+                    else rng.init(rp.seed, pixel, sample, segs);
                 } else {
                     ++depth;
+                    rng.init(rp.seed, pixel, sample, segs);
                     if (depth > 5 && (rng.next01() > 0.95f || depth > 1000)) alive = false; // :56-59
                 }
                 if (alive) {
                     const float r2scale = (rp.mode == VMN_MODE_FIXED) ? 1.f : 10.f;
                     float sc4[4] = {1.f, 1.f, 1.f, 1.f};
                     if (h.material && sc.tex) texture_sample(sc, h.uv0, h.uv1, sc4); // :62-80
-                    if (h.material && rng.next01() >= 0.96) { // mirror :98-109
-                        rng.skip(3);
+                    if (h.material && rng.next01() >= 0.96) { // mirror :98-109 (its three unused noise draws need no numbers)
                         nStart = h.P - rDir * 0.001f;
                         nDir = normalize(rDir - h.N * 2.f * dot(h.N, rDir));
                     } else {
@@ -283,8 +286,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                         } else {
                             r1d = 2 * 3.14159265358979323846 * xi1;
                             const double r2 = (double)r2scale * xi2;
-                            r2s = (float)sqrt(r2); sq = (float)sqrt(1 - r2);
-                            rng.skip(3); // :172-174 draw three unused numbers
+                            r2s = (float)sqrt(r2); sq = (float)sqrt(1 - r2); // (:172-174 draw three unused numbers)
                         }
                         double s1, c1;
                         sincos(r1d, &s1, &c1);
@@ -292,7 +294,6 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                         nStart = h.P - rDir * 0.001f;
                     }
                 }
-                mt.x = rng.draw;
             }
             mt.y = (depth & 0xFFFFu) | (segs << 16);
             radiance[slot] = acc;
