@@ -266,3 +266,34 @@ def test_progressive_accumulate_equals_one_shot(eng):
     assert np.array_equal(eng.read_image(engine.FILM_SUM), full)
     with pytest.raises(engine.VmnError):
         eng.render(mode=engine.MODE_COMPAT, seed=5, accumulate=True)
+
+
+@pytest.mark.parametrize("channels", [1, 3, 4])
+def test_textured_radiance_and_render_match_oracle(channels):
+    """N4 (SURVEY.md §8f): MeshEngine::boundTextures[0] scales the throughput at every diffuse triangle bounce (pathtracer.cpp:62-80,
+    VermiTexture::Sample meshEngine.cpp:21-46). Also the path whose throughput buffer is written (kThrWritten in k_shade)."""
+    pos, nrm, uv = scene_cornell()
+    rng = np.random.default_rng(5)
+    tex = rng.random((16, 8, channels), dtype=np.float32) * np.float32(1.5)
+    tex[3, 2] = np.float32(np.inf)  # a non-finite texel: inf * 0 = NaN must reach the radiance exactly where the reference's does
+    rays = rays_for("cornell", pos, 60_000, 23)
+    orc = checker.Oracle(pos, nrm, uv)
+    orc.set_texture(tex)
+    cam = engine.camera_from_settings(64, 64, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 3.6), 16)
+    with engine.Engine(device=0) as e:
+        e.set_scene(pos, nrm, uv, texture=tex)
+        for mode in (checker.MODE_COMPAT, checker.MODE_FIXED):
+            got, cnt = e.radiance(rays, 31, mode)
+            want, wcnt = orc.radiance(rays, 31, checker.RNG_PHILOX, mode)
+            same = ((got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))).all(1)
+            print("textured radiance mode", mode, "bit-exact", same.mean(), "nan paths", np.isnan(want).any(1).mean())
+            assert same.mean() >= 0.99 and (cnt == wcnt).mean() >= 0.99
+        e.set_camera(cam)
+        e.render(mode=engine.MODE_FIXED, seed=9)
+        img = e.read_image()
+    ref, _ = orc.render(_ocam(cam), checker.MODE_FIXED, checker.RNG_PHILOX, 9)
+    same = ((img.view(np.uint32) == ref.view(np.uint32)) | (np.isnan(img) & np.isnan(ref))).all(1)
+    print("textured render bit-exact pixels", same.mean())
+    assert same.mean() > 0.97
+    plain, _ = checker.Oracle(pos, nrm, uv).render(_ocam(cam), checker.MODE_FIXED, checker.RNG_PHILOX, 9)
+    assert not np.array_equal(plain, ref)  # the texture changes the picture

@@ -65,7 +65,7 @@ struct PathPool {
     DevBuf hit;       // float2 per queue entry: (t, original triangle id)
     DevBuf radiance;  // float4 per slot (rgb, first-hit distance / -100)
     DevBuf thr;       // float4 per slot
-    DevBuf meta;      // uint2 per slot: (draw counter, depth | segs<<16)
+    DevBuf meta;      // path tracer: uint32 per slot (depth 0..14 | throughput-written bit 15 | segments 16..31); BRUTEFORCE: uint2 per pixel
     DevBuf ctl;       // uint32 counters: [0..1] queue counts, [8..] claim counters (unsigned long long)
     DevBuf cstate;    // COMPAT per-local-pixel stratum state
     DevBuf bf_last;   // BRUTEFORCE per-local-pixel lastSampleColour (float4)
@@ -113,9 +113,11 @@ struct RoundParams {
     uint32_t max_segments;
 };
 
+constexpr uint32_t kThrWritten = 0x8000u; // path meta bit 15: thr[slot] holds the throughput (otherwise it is exactly (1,1,1,1))
+
 __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, RoundParams rp, const uint32_t* __restrict__ cstate,
                                                      float4* __restrict__ rays, uint32_t* __restrict__ qcount, float4* __restrict__ radiance,
-                                                     float4* __restrict__ thr, uint2* __restrict__ meta) {
+                                                     uint32_t* __restrict__ meta) {
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t total = rp.n_local * rp.batch;
     bool live = idx < total;
@@ -137,8 +139,7 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
         }
         // every slot of the round gets a defined state, live or not
         radiance[idx] = make_float4(0.f, 0.f, 0.f, live ? -100.f : 0.f);
-        thr[idx] = make_float4(1.f, 1.f, 1.f, 1.f);
-        meta[idx] = make_uint2(2u, live ? 0u : 0xFFFFFFFFu);
+        meta[idx] = 0u; // throughput = (1,1,1,1) until a textured bounce writes it (kThrWritten)
     }
     V3 o(0, 0, 0), d(0, 0, 0);
     if (live) {
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                                                     const float4* __restrict__ rays, const float2* __restrict__ hits,
                                                     const uint32_t* __restrict__ qcount_in, float4* __restrict__ rays_out,
                                                     uint32_t* __restrict__ qcount_out, float4* __restrict__ radiance, float4* __restrict__ thr,
-                                                    uint2* __restrict__ meta, int radiance_query) {
+                                                    uint32_t* __restrict__ meta, int radiance_query) {
     const uint32_t n = *qcount_in;
     const uint32_t lane = threadIdx.x & 31u;
     for (uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; base < n; base += (uint64_t)gridDim.x * blockDim.x) {
@@ -235,16 +236,24 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             slot = __float_as_uint(ra.w);
             V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
             const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y));
-            float4 acc = radiance[slot];
-            float4 tp = thr[slot];
-            uint2 mt = meta[slot];
-            uint32_t depth = mt.y & 0xFFFFu, segs = mt.y >> 16;
+            // Path state traffic: the throughput stays exactly (1,1,1,1) until a textured diffuse bounce scales it, and the radiance only
+            // changes on an emitter hit or at the first hit — so thr[] is not touched while kThrWritten is clear, and radiance[] is only
+            // read-modified-written when the sum can change (x + 1*0 = x; with a written throughput it may be non-finite, so always then).
+            uint32_t mt = meta[slot];
+            uint32_t depth = mt & 0x7FFFu, segs = mt >> 16;
+            const bool thr_written = (mt & kThrWritten) != 0u;
+            float4 tp = thr_written ? thr[slot] : make_float4(1.f, 1.f, 1.f, 1.f);
+            bool thr_dirty = false;
             ++segs;
             alive = true;
             if (!h.hit) alive = false; // :37-41
             if (alive) {
-                acc.x += tp.x * h.Le.x; acc.y += tp.y * h.Le.y; acc.z += tp.z * h.Le.z; acc.w += tp.w * 0.f; // :43
-                if (depth == 0) acc.w = h.dist; // :44-47
+                if (thr_written || depth == 0 || h.Le.x != 0.f || h.Le.y != 0.f || h.Le.z != 0.f) {
+                    float4 acc = radiance[slot];
+                    acc.x += tp.x * h.Le.x; acc.y += tp.y * h.Le.y; acc.z += tp.z * h.Le.z; acc.w += tp.w * 0.f; // :43
+                    if (depth == 0) acc.w = h.dist; // :44-47
+                    radiance[slot] = acc;
+                }
                 if (length(h.Le) > 1.f) alive = false; // :52
             }
             if (alive) {
@@ -278,7 +287,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                         double r1d;
                         float r2s, sq;
                         if (h.material) {
-                            tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3];
+                            if (sc.tex) { tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3]; thr_dirty = true; } // without a texture: * 1
                             const float r1 = (float)(2 * 3.14159265358979323846 * xi1);
                             const float r2 = (float)((double)r2scale * xi2);
                             r2s = sqrtf(r2); sq = sqrtf(1 - r2);
@@ -295,10 +304,8 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                     }
                 }
             }
-            mt.y = (depth & 0xFFFFu) | (segs << 16);
-            radiance[slot] = acc;
-            thr[slot] = tp;
-            meta[slot] = mt;
+            if (thr_dirty) thr[slot] = tp;
+            meta[slot] = (depth & 0x7FFFu) | ((thr_written || thr_dirty) ? kThrWritten : 0u) | (segs << 16);
         }
         const uint32_t ballot = __ballot_sync(0xffffffffu, alive);
         if (ballot) {
@@ -319,7 +326,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
 // FIXED: film[pixel] += the round's `batch` samples, in sample order.
 // COMPAT (batch = 1): additionally the early-out state machine of pathtracer.cpp:242-312.
 __global__ void __launch_bounds__(256) k_accumulate(PixelMap pm, RoundParams rp, uint32_t spp, const float4* __restrict__ radiance,
-                                                    const uint2* __restrict__ meta, float4* __restrict__ film, uint32_t* __restrict__ cstate,
+                                                    float4* __restrict__ film, uint32_t* __restrict__ cstate,
                                                     uint32_t* __restrict__ live_count) {
     const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (lp >= rp.n_local) return;
@@ -354,6 +361,13 @@ __global__ void __launch_bounds__(256) k_accumulate(PixelMap pm, RoundParams rp,
     if (!done) atomicAdd(live_count, 1u);
 }
 
+// std::max(std::min(x, 1.f), 0.f) as pathtracer.cpp:319-321 and integrators.cpp:177-179 evaluate it: std::min(a,b) = (b < a) ? b : a, std::max(a,b) = (a < b) ? b : a,
+// so a NaN mean stays NaN (fminf/fmaxf would drop it)
+__device__ __forceinline__ float clamp01_std(float x) {
+    const float m = (1.f < x) ? 1.f : x;
+    return (m < 0.f) ? 0.f : m;
+}
+
 // pathtracer.cpp:318-323 + camera.cpp:106-113
 __global__ void k_resolve(const float4* __restrict__ film, float* __restrict__ out, uint64_t npix) {
     const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -361,18 +375,11 @@ __global__ void k_resolve(const float4* __restrict__ film, float* __restrict__ o
     const float4 f = film[p];
     float* o = out + 5 * p;
     if (f.w == 0.f) { o[0] = o[1] = o[2] = o[3] = o[4] = 0.f; return; } // pixel not rendered by anyone
-    o[0] = fmaxf(fminf(f.x / f.w, 1.f), 0.f);
-    o[1] = fmaxf(fminf(f.y / f.w, 1.f), 0.f);
-    o[2] = fmaxf(fminf(f.z / f.w, 1.f), 0.f);
+    o[0] = clamp01_std(f.x / f.w);
+    o[1] = clamp01_std(f.y / f.w);
+    o[2] = clamp01_std(f.z / f.w);
     o[3] = 1.f;
     o[4] = f.w;
-}
-
-// std::max(std::min(x, 1.f), 0.f) as integrators.cpp:177-179 evaluates it: std::min(a,b) = (b < a) ? b : a, std::max(a,b) = (a < b) ? b : a,
-// so a NaN mean stays NaN (fminf/fmaxf would drop it)
-__device__ __forceinline__ float clamp01_std(float x) {
-    const float m = (1.f < x) ? 1.f : x;
-    return (m < 0.f) ? 0.f : m;
 }
 
 // integrators.cpp:176-183 + camera.cpp:106-113: BRUTEFORCE film (sum rgb, n) + (sum alpha, last primary distance) -> RGBAZ
@@ -403,7 +410,7 @@ __global__ void k_pack_rgba8(const float4* __restrict__ film, const float2* __re
             const float2 x = aux[p];
             r = clamp01_std(f.x / f.w); g = clamp01_std(f.y / f.w); b = clamp01_std(f.z / f.w); a = x.x / f.w; z = x.y;
         } else {
-            r = fmaxf(fminf(f.x / f.w, 1.f), 0.f); g = fmaxf(fminf(f.y / f.w, 1.f), 0.f); b = fmaxf(fminf(f.z / f.w, 1.f), 0.f); a = 1.f;
+            r = clamp01_std(f.x / f.w); g = clamp01_std(f.y / f.w); b = clamp01_std(f.z / f.w); a = 1.f;
         }
     }
     rgba[p] = make_uchar4((unsigned char)floorf(r * 255), (unsigned char)floorf(g * 255), (unsigned char)floorf(b * 255), (unsigned char)floorf(a * 255));
@@ -422,23 +429,22 @@ __global__ void k_camera_rays(CamDev cam, const uint64_t* __restrict__ pixel, co
 
 // vmn_radiance: turn caller rays into queue entries with slot = index
 __global__ void k_radiance_init(const float4* __restrict__ in, uint64_t n, float4* __restrict__ rays, float4* __restrict__ radiance,
-                                float4* __restrict__ thr, uint2* __restrict__ meta) {
+                                uint32_t* __restrict__ meta) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 a = in[2 * i], b = in[2 * i + 1];
     a.w = __uint_as_float((uint32_t)i); b.w = 0.f;
     rays[2 * i] = a; rays[2 * i + 1] = b;
     radiance[i] = make_float4(0.f, 0.f, 0.f, -100.f);
-    thr[i] = make_float4(1.f, 1.f, 1.f, 1.f);
-    meta[i] = make_uint2(2u, 0u);
+    meta[i] = 0u;
 }
 
-__global__ void k_radiance_out(const float4* __restrict__ radiance, const uint2* __restrict__ meta, uint64_t n, float4* __restrict__ out,
+__global__ void k_radiance_out(const float4* __restrict__ radiance, const uint32_t* __restrict__ meta, uint64_t n, float4* __restrict__ out,
                                uint32_t* __restrict__ rays_cast) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     out[i] = radiance[i];
-    rays_cast[i] = meta[i].y >> 16;
+    rays_cast[i] = meta[i] >> 16;
 }
 
 // ---- host orchestration ----------------------------------------------------------------------------
@@ -512,7 +518,7 @@ static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const Roun
     if (clk) clk->begin(ST_SHADE);
     k_shade<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
                                                          qc + cur, p->ray[cur ^ 1].as<float4>(), qc + (cur ^ 1), p->radiance.as<float4>(),
-                                                         p->thr.as<float4>(), p->meta.as<uint2>(), radiance_query);
+                                                         p->thr.as<float4>(), p->meta.as<uint32_t>(), radiance_query);
     if (clk) clk->end();
     VMN_CUDA(c, cudaGetLastError());
     ++c->stats.kernel_launches;
@@ -531,7 +537,7 @@ vmn_status launch_radiance(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint64
     uint32_t* qc = p->ctl.as<uint32_t>();
     VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 4096, c->stream));
     k_radiance_init<<<cdiv64(n, 256), 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_rays), n, p->ray[0].as<float4>(), p->radiance.as<float4>(),
-                                                           p->thr.as<float4>(), p->meta.as<uint2>());
+                                                           p->meta.as<uint32_t>());
     const uint32_t n32 = (uint32_t)n;
     VMN_CUDA(c, cudaMemcpyAsync(qc, &n32, 4, cudaMemcpyHostToDevice, c->stream));
     PixelMap pm{}; pm.width = 0xFFFFFFFFu; pm.height = 1;
@@ -548,7 +554,7 @@ vmn_status launch_radiance(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint64
         VMN_CUDA(c, cudaStreamSynchronize(c->stream));
         live = p->h_count[0];
     }
-    k_radiance_out<<<cdiv64(n, 256), 256, 0, c->stream>>>(p->radiance.as<float4>(), p->meta.as<uint2>(), n, reinterpret_cast<float4*>(d_out), d_rays_cast);
+    k_radiance_out<<<cdiv64(n, 256), 256, 0, c->stream>>>(p->radiance.as<float4>(), p->meta.as<uint32_t>(), n, reinterpret_cast<float4*>(d_out), d_rays_cast);
     VMN_CUDA(c, cudaGetLastError());
     c->stats.rays_traced = rays; c->stats.paths_traced = n; c->stats.kernel_launches += 2;
     return VMN_OK;
@@ -655,7 +661,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, p->cstate.as<uint32_t>(), p->ray[0].as<float4>(), qc,
-                                                                                   p->radiance.as<float4>(), p->thr.as<float4>(), p->meta.as<uint2>());
+                                                                                   p->radiance.as<float4>(), p->meta.as<uint32_t>());
                 clk.end();
                 ++c->stats.kernel_launches;
                 VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -673,7 +679,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 }
                 VMN_CUDA(c, cudaMemsetAsync(qc + 4, 0, 4, c->stream));
                 clk.begin(ST_RESOLVE);
-                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(), p->meta.as<uint2>(),
+                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(),
                                                                              c->film.as<float4>(), p->cstate.as<uint32_t>(), qc + 4);
                 clk.end();
                 ++c->stats.kernel_launches;
@@ -687,8 +693,8 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local * rp.batch, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, nullptr, p->ray[0].as<float4>(), qc,
-                                                                                              p->radiance.as<float4>(), p->thr.as<float4>(),
-                                                                                              p->meta.as<uint2>());
+                                                                                              p->radiance.as<float4>(),
+                                                                                              p->meta.as<uint32_t>());
                 clk.end();
                 ++c->stats.kernel_launches;
                 int cur = 0;
@@ -697,7 +703,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                     cur ^= 1;
                 }
                 clk.begin(ST_RESOLVE);
-                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(), p->meta.as<uint2>(),
+                k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(),
                                                                              c->film.as<float4>(), nullptr, nullptr);
                 clk.end();
                 ++c->stats.kernel_launches;
