@@ -184,6 +184,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: libraries that write there (NCCL prints its version line to stdout when NCCL_DEBUG is set)
+    # are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the B200 engine has no CPU fallback")
     torch.cuda.set_device(local)
@@ -326,10 +331,11 @@ def main():
                       "l2": "256 MiB L2 flush between timed steps", "paths_in_flight": args.max_paths},
            "spp_per_s": paths_all / npix / (ms / 1e3), "rays_per_step": rays_all / args.steps, "bvh_build_ms": build_ms,
            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(out))
     eng.close()
     if world > 1:
         dist.destroy_process_group()
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(out) + "\n").encode())
 
 
 if __name__ == "__main__":

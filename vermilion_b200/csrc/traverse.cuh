@@ -24,6 +24,12 @@ namespace vmn {
 #ifndef VMN_PREFETCH
 #define VMN_PREFETCH 0
 #endif
+#ifndef VMN_PREFETCH_RAYS
+#define VMN_PREFETCH_RAYS 0   // prefetch a claimed chunk of the ray queue into L2 (experiment)
+#endif
+#ifndef VMN_PREFETCH_TRIS
+#define VMN_PREFETCH_TRIS 0   // prefetch the first pending leaf triangle right after the node test (experiment)
+#endif
 #ifndef VMN_COOP_ATOMIC
 #define VMN_COOP_ATOMIC 1     // fold pooled triangle results with a shared 64-bit atomicMin per hit instead of a per-owner loop
 #endif
@@ -213,6 +219,9 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
 #endif
         s.ng = make_uint2(q1.x, (hitmask & 0xFF000000u) | (q0.w >> 24));
         s.tg = make_uint2(q1.y, hitmask & 0x00FFFFFFu);
+#if VMN_PREFETCH_TRIS
+        if (s.tg.y) asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.tris + s.tg.x + (__ffs(s.tg.y) - 1u)));
+#endif
 #if VMN_PREFETCH
         // the nearest internal child hit is the next node this ray visits (unless a triangle test culls it): start pulling it into L2
         // now, so that its DRAM latency overlaps the triangle phase instead of following it
@@ -367,7 +376,7 @@ __device__ __forceinline__ uint32_t trace_wide(const SceneDev& sc, V3 o, V3 d, f
 template <bool COUNT, class LoadRay, class StoreHit>
 __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n, unsigned long long* next, uint32_t chunk, uint32_t refill_min,
                                                  uint2* sstack, uint32_t sstride, uint32_t* wscratch, TravCounters* cnt, LoadRay load,
-                                                 StoreHit store) {
+                                                 StoreHit store, const void* rays_base = nullptr) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t FULL = 0xffffffffu;
     Trav s;
@@ -384,7 +393,19 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
                 if (lane == 0) b = atomicAdd(next, (unsigned long long)chunk);
                 b = __shfl_sync(FULL, b, 0);
                 if (b >= n) exhausted = true;
-                else { wbase = b; wleft = (uint32_t)((n - b < chunk) ? (n - b) : chunk); }
+                else {
+                    wbase = b; wleft = (uint32_t)((n - b < chunk) ? (n - b) : chunk);
+#if VMN_PREFETCH_RAYS
+                    for (uint32_t k = 4u * lane; k < wleft; k += 128u) { // one 128-byte line = four 32-byte rays
+                        const char* a = reinterpret_cast<const char*>(rays_base) + 32ull * (wbase + k);
+#if VMN_PREFETCH_RAYS == 2
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+#else
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+#endif
+                    }
+#endif
+                }
             }
             const uint32_t need = (uint32_t)__popc(idle);
             const uint32_t take = need < wleft ? need : wleft;

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev s
                             },
                             [&](uint64_t i, const Trav& s) {
                                 hits[i] = make_float2(s.best_t, __uint_as_float(leaf_original_id(sc.tris, s.best)));
-                            });
+                            }, rays);
     if (COUNT) { atomicAdd(&gcnt->nodes, cnt.nodes); atomicAdd(&gcnt->tris, cnt.tris); }
 }
 
