@@ -297,3 +297,16 @@ def test_textured_radiance_and_render_match_oracle(channels):
     assert same.mean() > 0.97
     plain, _ = checker.Oracle(pos, nrm, uv).render(_ocam(cam), checker.MODE_FIXED, checker.RNG_PHILOX, 9)
     assert not np.array_equal(plain, ref)  # the texture changes the picture
+
+
+def test_top_level_sah_rebuild_keeps_hits(monkeypatch):
+    """VMN_TOP_SAH=1 (experiment knob of the builder): another tree, the same closest hits."""
+    pos, nrm, uv = scenes.city(3, 3, 4, 2024)
+    rays = rays_for("city", pos, 100_000, 17)
+    ref = checker.Oracle(pos, nrm, uv).intersect(rays)
+    monkeypatch.setenv("VMN_TOP_SAH", "1")
+    with engine.Engine(device=0) as e:
+        e.set_scene(pos, nrm, uv)
+        c = common.classify_hits(e.intersect(rays), ref)
+    assert c["bad"] == 0 and c["tie"] + c["edge"] <= 2e-4 * len(rays), c
+    assert c["t_exact"] == c["hits"] and c["uv_err_max"] == 0.0, c

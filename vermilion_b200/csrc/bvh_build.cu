@@ -8,6 +8,9 @@
 //   4. k_leaves        leaf boxes + Morton-ordered 48-byte triangle records
 //   5. k_hierarchy     Karras 2012 binary radix tree, one thread per internal node
 //   6. k_refit         bottom-up boxes and subtree triangle counts, second-arrival atomics
+//   6b. top-level SAH  (experiment, env VMN_TOP_SAH=1, off by default — see top_sah_enabled) the top of the tree (the <= 1024 internal
+//                      nodes with the largest boxes) is replaced by a surface-area-heuristic tree built on the host over the subtrees
+//                      hanging below it (k_area_hist, k_top_collect, SahTop, k_top_scatter)
 //   7. k_collapse      level-synchronous collapse of the binary tree into 8-wide nodes
 //                      (greedy largest-surface-area expansion), octant-ordered child slots,
 //                      8-bit quantised child boxes -> 80-byte WideNode, leaf triangles re-laid out
@@ -15,7 +18,9 @@
 #include "engine.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <algorithm>
 #include <cfloat>
+#include <vector>
 
 namespace vmn {
 
@@ -189,15 +194,74 @@ __global__ void k_refit(int n, const int2* __restrict__ child, const int* __rest
     }
 }
 
-// ---- collapse to the compressed 8-wide BVH ----------------------------------------------------
-#define VMN_LEAF_MAX 3u // triangles per leaf slot (unary 3-bit count in meta)
 
-struct CollapseCtl { uint32_t n_nodes, n_tris, q_out, pad; };
-
+// ---- top-level SAH rebuild -----------------------------------------------------------------------
+// Half-octave bin of a box area relative to the root's: 0 = as large as the root, 127 = tiny. Areas shrink monotonically from parent to
+// child (nested boxes), so "bin <= b" selects a connected top part T of the tree; the nodes hanging directly below T are the cut.
 __device__ __forceinline__ float box_area(float4 a, float4 b) {
     float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
     return dx * dy + dy * dz + dz * dx;
 }
+__device__ __forceinline__ int area_bin(float a, float root_area) {
+    if (!(a > 0.f) || !(root_area > 0.f)) return 127;
+    if (a >= root_area) return 0;
+    const float v = -2.f * log2f(a / root_area);
+    return v >= 127.f ? 127 : (int)v;
+}
+
+__global__ void k_area_hist(int nint, const float4* __restrict__ bmin, const float4* __restrict__ bmax, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[128];
+    if (threadIdx.x < 128) sh[threadIdx.x] = 0;
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const float ra = box_area(bmin[0], bmax[0]);
+    if (i < nint) atomicAdd(&sh[area_bin(box_area(bmin[i], bmax[i]), ra)], 1u);
+    __syncthreads();
+    if (threadIdx.x < 128 && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
+}
+
+struct CutRec { uint32_t id, count; float lo[3], hi[3]; };        // a subtree below the top part
+struct TopRec { uint32_t slot, left, right, count; float lo[3], hi[3]; }; // a rebuilt top node, written into the slot of an old one
+
+__global__ void k_top_collect(int n, int bin_max, const int* __restrict__ parent, const float4* __restrict__ bmin,
+                              const float4* __restrict__ bmax, const uint32_t* __restrict__ count, uint32_t* __restrict__ ctr,
+                              uint32_t* __restrict__ top_ids, CutRec* __restrict__ cut, uint32_t cap) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nint = n - 1;
+    if (i >= 2 * n - 1) return;
+    const float ra = box_area(bmin[0], bmax[0]);
+    const float4 lo = bmin[i], hi = bmax[i];
+    const bool in_top = i < nint && area_bin(box_area(lo, hi), ra) <= bin_max;
+    if (in_top) {
+        const uint32_t k = atomicAdd(&ctr[0], 1u);
+        if (k < cap) top_ids[k] = (uint32_t)i;
+        return;
+    }
+    const int p = parent[i];
+    if (p < 0 || area_bin(box_area(bmin[p], bmax[p]), ra) > bin_max) return;
+    const uint32_t k = atomicAdd(&ctr[1], 1u);
+    if (k > cap) return;
+    CutRec r;
+    r.id = (uint32_t)i; r.count = count[i];
+    r.lo[0] = lo.x; r.lo[1] = lo.y; r.lo[2] = lo.z; r.hi[0] = hi.x; r.hi[1] = hi.y; r.hi[2] = hi.z;
+    cut[k] = r;
+}
+
+__global__ void k_top_scatter(uint32_t m, const TopRec* __restrict__ rec, int2* __restrict__ child, float4* __restrict__ bmin,
+                              float4* __restrict__ bmax, uint32_t* __restrict__ count) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    const TopRec r = rec[k];
+    child[r.slot] = make_int2((int)r.left, (int)r.right);
+    bmin[r.slot] = make_float4(r.lo[0], r.lo[1], r.lo[2], 0.f);
+    bmax[r.slot] = make_float4(r.hi[0], r.hi[1], r.hi[2], 0.f);
+    count[r.slot] = r.count;
+}
+
+// ---- collapse to the compressed 8-wide BVH ----------------------------------------------------
+#define VMN_LEAF_MAX 3u // triangles per leaf slot (unary 3-bit count in meta)
+
+struct CollapseCtl { uint32_t n_nodes, n_tris, q_out, pad; };
 
 // One thread turns one binary subtree root into one WideNode and enqueues its internal children.
 __global__ void k_collapse(const uint2* __restrict__ q_in, uint32_t n_in, uint2* __restrict__ q_out, CollapseCtl* ctl, int n,
@@ -319,6 +383,141 @@ __global__ void k_collapse(const uint2* __restrict__ q_in, uint32_t n_in, uint2*
     nodes[widx] = nd;
 }
 
+// Host side of the top-level rebuild: a binary SAH tree (full sweep on all three axes, cost = area x triangle count) over the cut
+// subtrees. Internal nodes take the slots of the old top nodes in preorder, so the root stays binary node 0. Below depth 20 the split is
+// the count median along the widest centroid axis, which bounds the depth of the rebuilt part (the traversal stacks are finite).
+namespace {
+struct HBox {
+    float lo[3], hi[3];
+    void reset() { for (int a = 0; a < 3; ++a) { lo[a] = FLT_MAX; hi[a] = -FLT_MAX; } }
+    void grow(const float* l, const float* h) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], l[a]); hi[a] = std::max(hi[a], h[a]); } }
+    float area() const { float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2]; return dx * dy + dy * dz + dz * dx; }
+};
+
+struct SahTop {
+    const std::vector<CutRec>& cut;
+    const std::vector<uint32_t>& slots;
+    std::vector<TopRec>& out;
+    std::vector<uint32_t> idx;
+    std::vector<float> right_area;
+    std::vector<uint64_t> right_count;
+    size_t next_slot = 0;
+
+    SahTop(const std::vector<CutRec>& c, const std::vector<uint32_t>& s, std::vector<TopRec>& o) : cut(c), slots(s), out(o) {
+        idx.resize(cut.size());
+        for (size_t i = 0; i < idx.size(); ++i) idx[i] = (uint32_t)i;
+        right_area.resize(cut.size() + 1); right_count.resize(cut.size() + 1);
+    }
+    void sort_axis(size_t lo, size_t hi, int axis) {
+        std::sort(idx.begin() + lo, idx.begin() + hi, [&](uint32_t a, uint32_t b) {
+            const float ca = cut[a].lo[axis] + cut[a].hi[axis], cb = cut[b].lo[axis] + cut[b].hi[axis];
+            return ca < cb || (ca == cb && cut[a].id < cut[b].id);
+        });
+    }
+    // returns the binary node id of the subtree over idx[lo, hi)
+    uint32_t build(size_t lo, size_t hi, int depth, HBox* box, uint64_t* count) {
+        if (hi - lo == 1) {
+            const CutRec& r = cut[idx[lo]];
+            box->reset(); box->grow(r.lo, r.hi); *count = r.count;
+            return r.id;
+        }
+        const size_t k = next_slot++;
+        out.emplace_back();
+        int best_axis = 0; size_t best_pos = lo + (hi - lo) / 2;
+        if (depth < 20) {
+            float best_cost = FLT_MAX;
+            for (int axis = 0; axis < 3; ++axis) {
+                sort_axis(lo, hi, axis);
+                HBox b; b.reset(); uint64_t c = 0;
+                for (size_t i = hi; i-- > lo;) { b.grow(cut[idx[i]].lo, cut[idx[i]].hi); c += cut[idx[i]].count; right_area[i] = b.area(); right_count[i] = c; }
+                b.reset(); c = 0;
+                for (size_t i = lo; i + 1 < hi; ++i) {
+                    b.grow(cut[idx[i]].lo, cut[idx[i]].hi); c += cut[idx[i]].count;
+                    const float cost = b.area() * (float)c + right_area[i + 1] * (float)right_count[i + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_pos = i + 1; }
+                }
+            }
+            if (best_axis != 2) sort_axis(lo, hi, best_axis);
+        } else {
+            HBox cb; cb.reset(); uint64_t total = 0;
+            for (size_t i = lo; i < hi; ++i) {
+                const CutRec& r = cut[idx[i]];
+                const float c3[3] = {r.lo[0] + r.hi[0], r.lo[1] + r.hi[1], r.lo[2] + r.hi[2]};
+                cb.grow(c3, c3); total += r.count;
+            }
+            for (int a = 1; a < 3; ++a) if (cb.hi[a] - cb.lo[a] > cb.hi[best_axis] - cb.lo[best_axis]) best_axis = a;
+            sort_axis(lo, hi, best_axis);
+            uint64_t c = 0; best_pos = lo + 1;
+            for (size_t i = lo; i + 1 < hi; ++i) { c += cut[idx[i]].count; best_pos = i + 1; if (2 * c >= total) break; }
+        }
+        HBox bl, br; uint64_t cl = 0, cr = 0;
+        const uint32_t left = build(lo, best_pos, depth + 1, &bl, &cl);
+        const uint32_t right = build(best_pos, hi, depth + 1, &br, &cr);
+        *box = bl; box->grow(br.lo, br.hi); *count = cl + cr;
+        TopRec& r = out[k];
+        r.slot = slots[k]; r.left = left; r.right = right;
+        // a rebuilt node never becomes a leaf slot of the wide tree: its triangles are not contiguous in the sorted order
+        r.count = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(*count, 4), 0xFFFFFFFFull);
+        for (int a = 0; a < 3; ++a) { r.lo[a] = box->lo[a]; r.hi[a] = box->hi[a]; }
+        return r.slot;
+    }
+};
+constexpr uint32_t kTopCap = 1024; // internal nodes in the rebuilt top part
+} // namespace
+
+// Off by default (env VMN_TOP_SAH=1 turns it on, read at every commit). Measured on B200 (profiles/r01u_stats_*.jsonl): C2 spheres 4.37 ->
+// 4.15 nodes per ray, k_extend -3 %; but the C4 city goes from 15.2 nodes + 5.3 triangles per ray to 22.1 + 8.9 (k_extend +49 %): the
+// traversal visits children in a fixed octant order, which matches the 2x2x2 arrangement that three Morton median splits produce and
+// is a poor front-to-back proxy for the slab-like partitions the SAH picks.
+static bool top_sah_enabled() {
+    const char* e = getenv("VMN_TOP_SAH");
+    return e && e[0] == '1';
+}
+
+// replaces the top of the binary tree in place; leaves it untouched when the tree is too small or degenerate
+static vmn_status rebuild_top(vmn_ctx* c, uint32_t n, DevBuf& scratch, const int* parent, uint32_t* count) {
+    cudaStream_t st = c->stream;
+    if (n < 64 || !top_sah_enabled()) return VMN_OK;
+    const size_t off_hist = 0, off_ctr = 512, off_top = 1024, off_cut = off_top + 4 * kTopCap, off_rec = off_cut + sizeof(CutRec) * (kTopCap + 2);
+    vmn_status s = dev_reserve(c, scratch, off_rec + sizeof(TopRec) * kTopCap);
+    if (s != VMN_OK) return s;
+    char* base = scratch.as<char>();
+    VMN_CUDA(c, cudaMemsetAsync(base, 0, 1024, st));
+    const float4* bmin = c->b_min.as<float4>(); const float4* bmax = c->b_max.as<float4>();
+    k_area_hist<<<(n - 1 + 255) / 256, 256, 0, st>>>((int)n - 1, bmin, bmax, reinterpret_cast<uint32_t*>(base + off_hist));
+    uint32_t hist[128];
+    VMN_CUDA(c, cudaMemcpyAsync(hist, base + off_hist, sizeof(hist), cudaMemcpyDeviceToHost, st));
+    VMN_CUDA(c, cudaStreamSynchronize(st));
+    int bin_max = -1; uint64_t cum = 0;
+    for (int b = 0; b < 128; ++b) { cum += hist[b]; if (cum > kTopCap) break; bin_max = b; }
+    if (bin_max < 0) return VMN_OK; // more than kTopCap boxes as large as the root's: nothing sensible to rebuild
+    k_top_collect<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>((int)n, bin_max, parent, bmin, bmax, count, reinterpret_cast<uint32_t*>(base + off_ctr),
+                                                           reinterpret_cast<uint32_t*>(base + off_top), reinterpret_cast<CutRec*>(base + off_cut), kTopCap);
+    uint32_t ctr[2] = {0, 0};
+    VMN_CUDA(c, cudaMemcpyAsync(ctr, base + off_ctr, sizeof(ctr), cudaMemcpyDeviceToHost, st));
+    VMN_CUDA(c, cudaStreamSynchronize(st));
+    if (ctr[0] < 2 || ctr[0] > kTopCap || ctr[1] != ctr[0] + 1) return VMN_OK;
+    std::vector<uint32_t> slots(ctr[0]);
+    std::vector<CutRec> cut(ctr[1]);
+    VMN_CUDA(c, cudaMemcpyAsync(slots.data(), base + off_top, 4 * slots.size(), cudaMemcpyDeviceToHost, st));
+    VMN_CUDA(c, cudaMemcpyAsync(cut.data(), base + off_cut, sizeof(CutRec) * cut.size(), cudaMemcpyDeviceToHost, st));
+    VMN_CUDA(c, cudaStreamSynchronize(st));
+    std::sort(slots.begin(), slots.end()); // the atomics hand out positions in any order: sort for a reproducible tree (slot 0 = root first)
+    std::sort(cut.begin(), cut.end(), [](const CutRec& a, const CutRec& b) { return a.id < b.id; });
+    if (slots[0] != 0u) return VMN_OK;
+    std::vector<TopRec> recs;
+    recs.reserve(slots.size());
+    SahTop sah(cut, slots, recs);
+    HBox box; uint64_t total = 0;
+    sah.build(0, cut.size(), 0, &box, &total);
+    if (recs.size() != slots.size()) return fail(c, VMN_ERR_STATE, "top-level rebuild produced %zu of %zu nodes", recs.size(), slots.size());
+    VMN_CUDA(c, cudaMemcpyAsync(base + off_rec, recs.data(), sizeof(TopRec) * recs.size(), cudaMemcpyHostToDevice, st));
+    k_top_scatter<<<((uint32_t)recs.size() + 127) / 128, 128, 0, st>>>((uint32_t)recs.size(), reinterpret_cast<const TopRec*>(base + off_rec),
+                                                                     c->b_child.as<int2>(), c->b_min.as<float4>(), c->b_max.as<float4>(), count);
+    VMN_CUDA(c, cudaStreamSynchronize(st)); // recs is a host temporary
+    return VMN_OK;
+}
+
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
 vmn_status build_bvh(vmn_ctx* c) {
@@ -340,7 +539,7 @@ vmn_status build_bvh(vmn_ctx* c) {
     DevBuf &pmin = c->build_scratch[0], &pmax = c->build_scratch[1], &keys = c->build_scratch[2], &keys2 = c->build_scratch[3],
            &vals = c->build_scratch[4], &vals2 = c->build_scratch[5], &parent = c->build_scratch[6], &first = c->build_scratch[7],
            &count = c->build_scratch[8], &flags = c->build_scratch[9], &sb = c->build_scratch[10], &tmp = c->build_scratch[11],
-           &qa = c->build_scratch[12], &qb = c->build_scratch[13], &ctl = c->build_scratch[14];
+           &qa = c->build_scratch[12], &qb = c->build_scratch[13], &ctl = c->build_scratch[14], &top = c->build_scratch[15];
     vmn_status s = VMN_OK;
     auto cleanup = [&]() {};
 #define TRY(x) do { s = (x); if (s != VMN_OK) { cleanup(); return s; } } while (0)
@@ -381,6 +580,7 @@ vmn_status build_bvh(vmn_ctx* c) {
                                           count.as<uint32_t>(), flags.as<uint32_t>());
     }
     TRYCUDA(cudaGetLastError());
+    if (n > 1) TRY(rebuild_top(c, n, top, parent.as<int>(), count.as<uint32_t>()));
 
     // level-synchronous collapse; queue capacity = number of internal binary nodes (+1)
     TRY(dev_alloc(c, qa, 8ull * n)); TRY(dev_alloc(c, qb, 8ull * n));

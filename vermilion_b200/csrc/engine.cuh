@@ -38,7 +38,7 @@ struct vmn_ctx {
     // built scene
     vmn::DevBuf tris, tris_sorted, tris_orig, shade, wide, b_min, b_max, b_child;
     vmn::DevBuf spheres, tex, tex1;
-    vmn::DevBuf build_scratch[15]; // bvh_build.cu, grow-only
+    vmn::DevBuf build_scratch[16]; // bvh_build.cu, grow-only
     uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0, tex1_w = 0, tex1_h = 0, tex1_c = 0;
     bool have_tex = false, have_tex1 = false;
     uint64_t n_wide = 0;
