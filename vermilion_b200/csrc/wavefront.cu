@@ -138,8 +138,7 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
             }
         }
         // every slot of the round gets a defined state, live or not
-        radiance[idx] = make_float4(0.f, 0.f, 0.f, live ? -100.f : 0.f);
-        meta[idx] = 0u; // throughput = (1,1,1,1) until a textured bounce writes it (kThrWritten)
+        meta[idx] = 0u; // radiance[idx] is first written by the path's first k_shade iteration; throughput = (1,1,1,1) until a textured bounce writes it (kThrWritten)
     }
     V3 o(0, 0, 0), d(0, 0, 0);
     if (live) {
@@ -249,12 +248,15 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             if (!h.hit) alive = false; // :37-41
             if (alive) {
                 if (thr_written || depth == 0 || h.Le.x != 0.f || h.Le.y != 0.f || h.Le.z != 0.f) {
-                    float4 acc = radiance[slot];
+                    // the first iteration of a path starts from accumColour = (0,0,0,-100) (pathtracer.cpp:26): nothing to read
+                    float4 acc = depth == 0 ? make_float4(0.f, 0.f, 0.f, -100.f) : radiance[slot];
                     acc.x += tp.x * h.Le.x; acc.y += tp.y * h.Le.y; acc.z += tp.z * h.Le.z; acc.w += tp.w * 0.f; // :43
                     if (depth == 0) acc.w = h.dist; // :44-47
                     radiance[slot] = acc;
                 }
                 if (length(h.Le) > 1.f) alive = false; // :52
+            } else if (depth == 0) {
+                radiance[slot] = make_float4(0.f, 0.f, 0.f, -100.f); // a primary ray that leaves the scene (:37-41 returns the initial value)
             }
             if (alive) {
                 // pixel/sample of this slot (Philox counter)
@@ -435,7 +437,6 @@ __global__ void k_radiance_init(const float4* __restrict__ in, uint64_t n, float
     float4 a = in[2 * i], b = in[2 * i + 1];
     a.w = __uint_as_float((uint32_t)i); b.w = 0.f;
     rays[2 * i] = a; rays[2 * i + 1] = b;
-    radiance[i] = make_float4(0.f, 0.f, 0.f, -100.f);
     meta[i] = 0u;
 }
 
