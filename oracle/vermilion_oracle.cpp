@@ -603,7 +603,7 @@ inline float std_max(float a, float b) { return (a < b) ? b : a; } // std::max(a
 
 template <class Rng>
 uint64_t render_pixel_bf(const orc_scene& sc, const orc_camera& cam, const M4& M, uint64_t p, uint32_t flags, Rng& rng, float* px5,
-                         uint32_t* samples_taken) {
+                         uint32_t* samples_taken, float* raw6 = nullptr) {
     const V3 lightLocation(500, 1100, 2000); // :16
     uint64_t nrays = 0;
     V4 accum{0, 0, 0, 0}, last{0, 0, 0, 0}, cur{0, 0, 0, 0};
@@ -669,6 +669,7 @@ uint64_t render_pixel_bf(const orc_scene& sc, const orc_camera& cam, const M4& M
     px5[3] = accum.w / nTotalSamples;
     px5[4] = hitDistance;
     if (samples_taken) *samples_taken = nTotalSamples;
+    if (raw6) { raw6[0] = accum.x; raw6[1] = accum.y; raw6[2] = accum.z; raw6[3] = (float)nTotalSamples; raw6[4] = accum.w; raw6[5] = hitDistance; }
     return nrays;
 }
 
@@ -811,21 +812,21 @@ uint64_t orc_render(const orc_scene* s, const orc_camera* cam, int mode, int rng
 }
 
 uint64_t orc_render_bruteforce(const orc_scene* s, const orc_camera* cam, int rng_kind, uint64_t seed, uint32_t flags, uint64_t p0,
-                                uint64_t p1, float* image, uint32_t* samples_taken, int threads) {
+                                uint64_t p1, float* image, uint32_t* samples_taken, float* raw, int threads) {
     M4 M = camera_matrix(*cam);
     uint64_t total = 0;
     if (rng_kind == ORC_RNG_MT32_SHARED) { // sequential by construction: one engine, pixels in order
         std::mt19937 eng((uint32_t)seed);
         RngMt32Shared rng(eng);
         for (uint64_t p = p0; p < p1; ++p)
-            total += render_pixel_bf(*s, *cam, M, p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr);
+            total += render_pixel_bf(*s, *cam, M, p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr, raw ? raw + 6 * (size_t)p : nullptr);
         return total;
     }
     threads = clamp_threads(threads);
 #pragma omp parallel for schedule(dynamic, 16) num_threads(threads) reduction(+ : total)
     for (int64_t p = (int64_t)p0; p < (int64_t)p1; ++p) {
         RngPhilox rng(seed, (uint64_t)p);
-        total += render_pixel_bf(*s, *cam, M, (uint64_t)p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr);
+        total += render_pixel_bf(*s, *cam, M, (uint64_t)p, flags, rng, image + 5 * (size_t)p, samples_taken ? samples_taken + p : nullptr, raw ? raw + 6 * (size_t)p : nullptr);
     }
     return total;
 }

@@ -115,9 +115,10 @@ uint64_t orc_render(const orc_scene*, const orc_camera*, int mode, int rng_kind,
  * shared by all pixels, drawn in pixel order (what the reference does with one OpenMP thread; its seed is time(0),
  * integrators.cpp:30). PHILOX: stream (seed, pixel, sample), draws 0 and 1. image: 5 floats per pixel = clamped rgb,
  * alpha = hits / samples, depth = distance of the last primary RayCast (integrators.cpp:176-183). samples_taken
- * (optional): nTotalSamples per pixel. Returns the number of BVH queries made. */
+ * (optional): nTotalSamples per pixel. raw (optional): 6 floats per pixel = the un-normalised state (sum r, sum g, sum b, n,
+ * sum alpha, last distance), i.e. the two film planes of the GPU engine. Returns the number of BVH queries made. */
 uint64_t orc_render_bruteforce(const orc_scene*, const orc_camera*, int rng_kind, uint64_t seed, uint32_t flags, uint64_t p0,
-                               uint64_t p1, float* image, uint32_t* samples_taken, int threads);
+                               uint64_t p1, float* image, uint32_t* samples_taken, float* raw, int threads);
 
 /* Counter-based RNG shared by the oracle's PHILOX mode and the GPU path:
  * Philox4x32-10, key (seed_lo, seed_hi), counter (pixel_lo, pixel_hi, sample, draw/4). */

@@ -104,7 +104,7 @@ class Oracle:
             L.orc_scene_add_texture.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
             L.orc_render_bruteforce.restype = C.c_uint64
             L.orc_render_bruteforce.argtypes = [C.c_void_p, C.POINTER(OrcCamera), C.c_int, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64,
-                                                C.c_void_p, C.c_void_p, C.c_int]
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
             L.orc_philox.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
             L.orc_max_threads.restype = C.c_int
             cls._lib = L
@@ -135,14 +135,15 @@ class Oracle:
         h, w, c = tex.shape
         self.lib().orc_scene_add_texture(self.h, _p(tex), w, h, c)
 
-    def render_bruteforce(self, cam, rng=RNG_PHILOX, seed=1, flags=0, p0=0, p1=None, threads=0):
-        """BruteForceTracer::Render restated: (image[npix,5], samples_taken[npix], BVH queries)"""
+    def render_bruteforce(self, cam, rng=RNG_PHILOX, seed=1, flags=0, p0=0, p1=None, threads=0, want_raw=False):
+        """BruteForceTracer::Render restated: (image[npix,5], samples_taken[npix], BVH queries[, raw[npix,6]])"""
         npx = cam.width * cam.height
         p1 = npx if p1 is None else p1
         img = np.zeros((npx, 5), np.float32)
         taken = np.zeros(npx, np.uint32)
-        n = self.lib().orc_render_bruteforce(self.h, C.byref(cam), rng, seed, flags, p0, p1, _p(img), _p(taken), threads)
-        return img, taken, n
+        raw = np.zeros((npx, 6), np.float32) if want_raw else None
+        n = self.lib().orc_render_bruteforce(self.h, C.byref(cam), rng, seed, flags, p0, p1, _p(img), _p(taken), _p(raw), threads)
+        return (img, taken, n, raw) if want_raw else (img, taken, n)
 
     def stats(self):
         a, b = C.c_uint32(), C.c_uint32()

@@ -68,6 +68,38 @@ def test_two_ranks_reassemble_the_frame(tmp_path, split):
     assert raw[:, :3].max() > 0
 
 
+def _worker_bf(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pos, nrm, uv = scenes.cornell()
+        cs = checker.camera_settings(W, H, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 2.16), SPP)
+        _, _, _, raw = checker.Oracle(pos, nrm, uv, spheres=False).render_bruteforce(checker.camera_fields_py(cs), seed=SEED, want_raw=True)
+        p = vd.render_params("tile", rank, world, 0, tile=8)
+        own = vd.tile_owner_map(W, H, p["tile_size"], p["tile_world"]).reshape(-1) == p["tile_rank"]
+        raw[~own] = 0.0  # what a rank's two film planes hold outside its tiles
+        film, aux = torch.from_numpy(raw[:, :4].copy()), torch.from_numpy(raw[:, 4:].copy())
+        vd.reduce_film(film)
+        vd.reduce_film(aux)
+        np.save(os.path.join(out_dir, f"bf_{rank}.npy"), vd.resolve_bruteforce(film.numpy(), aux.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_reassemble_the_bruteforce_frame(tmp_path):
+    """BruteForceTracer splits by tiles; its second film plane (sum alpha, last distance — inf where the open Cornell box lets a primary
+    ray escape) is reduced with the first; the resolved frame equals the single-process oracle image bit for bit."""
+    world = 2
+    mp.spawn(_worker_bf, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    imgs = [np.load(tmp_path / f"bf_{r}.npy") for r in range(world)]
+    pos, nrm, uv = scenes.cornell()
+    cs = checker.camera_settings(W, H, (0, 275, 1100), (0, 0, 0), 6.0, (3.6, 2.16), SPP)
+    want, _, _ = checker.Oracle(pos, nrm, uv, spheres=False).render_bruteforce(checker.camera_fields_py(cs), seed=SEED)
+    for im in imgs:
+        assert np.array_equal(im.view(np.uint32), want.view(np.uint32))
+    assert (want[:, 3] > 0).any() and want[:, :3].max() > 0
+
+
 def test_partitions_cover_exactly_once():
     for world in (1, 2, 3, 4, 8):
         for spp in (1, 7, 64, 4096):

@@ -63,6 +63,25 @@ def resolve(film_sum):
     return out
 
 
+def resolve_bruteforce(film_sum, film_aux):
+    """BRUTEFORCE film planes -> RGBAZ rows as k_resolve_bf / integrators.cpp:176-183 do: std::max(std::min(x, 1), 0) keeps a NaN mean,
+    alpha = sum alpha / n, depth = distance of the last primary RayCast (numpy, host side; tests and tools only)."""
+    f = np.asarray(film_sum, np.float32).reshape(-1, 4)
+    a = np.asarray(film_aux, np.float32).reshape(-1, 2)
+    out = np.zeros((len(f), 5), np.float32)
+    n = f[:, 3]
+    ok = n > 0
+    with np.errstate(invalid="ignore", divide="ignore"):
+        rgb = f[:, :3] / n[:, None]
+        m = np.where(1.0 < rgb, np.float32(1.0), rgb)      # std::min(x, 1.f) = (1 < x) ? 1 : x
+        rgb = np.where(m < 0.0, np.float32(0.0), m)         # std::max(m, 0.f) = (m < 0) ? 0 : m
+        alpha = a[:, 0] / n
+    out[ok, :3] = rgb[ok]
+    out[ok, 3] = alpha[ok]
+    out[ok, 4] = a[ok, 1]
+    return out
+
+
 def device_film_tensor(eng, device):
     """torch view (no copy) of the context's device film buffer, for NCCL."""
     import torch
@@ -74,6 +93,31 @@ def device_film_tensor(eng, device):
     h = _Holder()
     h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3}
     return torch.as_tensor(h, device=device)
+
+
+def device_film_aux_tensor(eng, device):
+    """torch view (no copy) of the second plane of a BRUTEFORCE film (sum alpha, last distance), for NCCL."""
+    import torch
+    ptr, n = eng.film_aux_device()
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3}
+    return torch.as_tensor(h, device=device)
+
+
+def render_bruteforce_distributed(eng, device, seed, rank, world, tile=64, shadow=False, group=None):
+    """BruteForceTracer across ranks: interleaved tiles (its early-out is sequential per pixel, so pixels — not samples — are split);
+    both film planes are zero outside a rank's tiles, so two all-reduce(SUM) assemble the frame exactly. Returns RGBAZ (every rank)."""
+    from . import engine as _engine
+    eng.render(mode=_engine.MODE_BRUTEFORCE, seed=seed, shadow=shadow, **render_params("tile", rank, world, 0, tile))
+    film = device_film_tensor(eng, device)
+    aux = device_film_aux_tensor(eng, device)
+    reduce_film(film, group)
+    reduce_film(aux, group)
+    return eng.resolve_device(film.data_ptr())  # the context resolves with its own (now reduced) second plane
 
 
 def render_distributed(eng, device, mode, seed, split, rank, world, spp_total, max_segments=5, tile=64, group=None):
