@@ -665,19 +665,22 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                                                                                    p->radiance.as<float4>(), p->meta.as<uint32_t>());
                 clk.end();
                 ++c->stats.kernel_launches;
-                VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
-                VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-                uint64_t live = p->h_count[0];
-                c->stats.paths_traced += live;
+                VMN_CUDA(c, cudaMemcpyAsync(p->h_count + 2, qc, 4, cudaMemcpyDeviceToHost, c->stream)); // samples started; read after the next sync
                 int cur = 0;
-                for (uint32_t it = 0; live; ++it) {
-                    if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
-                    if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
-                    cur ^= 1;
+                uint64_t live = 1;
+                for (uint32_t it = 0; live;) {
+                    // four bounces per host round trip: the queue counts live on the device and a kernel that finds its queue empty returns
+                    // at once, so the only thing the host needs is to know when to stop
+                    for (int k = 0; k < 4; ++k, ++it) {
+                        if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
+                        if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
+                        cur ^= 1;
+                    }
                     VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + cur, 4, cudaMemcpyDeviceToHost, c->stream));
                     VMN_CUDA(c, cudaStreamSynchronize(c->stream));
                     live = p->h_count[0];
                 }
+                c->stats.paths_traced += p->h_count[2];
                 VMN_CUDA(c, cudaMemsetAsync(qc + 4, 0, 4, c->stream));
                 clk.begin(ST_RESOLVE);
                 k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(),
