@@ -164,8 +164,10 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
         const uint32_t rel = __popc(s.ng.y & 0xFFu & ((1u << slot) - 1u));
         const uint32_t nidx = s.ng.x + rel;
         if (s.ng.y & 0xFF000000u) { // siblings still pending
-            if (s.sp < VMN_SH_STACK) sstack[s.sp * sstride] = s.ng; else lstack[s.sp - VMN_SH_STACK] = s.ng;
-            ++s.sp;
+            // one entry per level at most, so 64 entries cover any tree the builder makes (depth <= 63 Morton bits); the bound only
+            // keeps a corrupt tree from writing outside the array
+            if (s.sp < VMN_SH_STACK) { sstack[s.sp * sstride] = s.ng; ++s.sp; }
+            else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
         }
         const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
         const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
