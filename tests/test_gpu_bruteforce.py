@@ -122,3 +122,24 @@ def test_bruteforce_argument_errors():
             eng.set_texture(2, np.zeros((2, 2, 3), np.float32))
         eng.render(mode=engine.MODE_BRUTEFORCE)
         assert eng.read_image().shape == (64, 5)
+
+
+def test_empty_scene_renders_only_the_room_spheres():
+    """No triangles at all: MeshEngine::RayCast still answers with the eight spheres; both integrators match the oracle bit for bit."""
+    cam = engine.camera_from_settings(48, 32, (0, 500, 1900), (0, 0, 0), 6.0, (3.6, 2.4), 8)
+    orc = checker.Oracle(np.zeros((0, 9), np.float32))
+    with engine.Engine(device=0) as eng:
+        eng.set_scene(np.zeros((0, 9), np.float32))
+        eng.set_camera(cam)
+        eng.render(mode=engine.MODE_BRUTEFORCE, seed=3)
+        bf = eng.read_image()
+        eng.render(mode=engine.MODE_FIXED, seed=3)
+        pt = eng.read_image()
+        eng.render(mode=engine.MODE_COMPAT, seed=3)
+        pc = eng.read_image()
+    ref, _, _ = orc.render_bruteforce(_ocam(cam), seed=3)
+    assert np.array_equal(_bits(bf), _bits(ref))
+    want, _ = orc.render(_ocam(cam), checker.MODE_FIXED, checker.RNG_PHILOX, 3)
+    assert np.array_equal(_bits(pt), _bits(want))
+    want, _ = orc.render(_ocam(cam), checker.MODE_COMPAT, checker.RNG_PHILOX, 3)
+    assert np.array_equal(_bits(pc), _bits(want))
