@@ -102,7 +102,7 @@ struct SceneDev {
     uint32_t tex1_w, tex1_h, tex1_c;
 };
 
-struct SphereDev { float cx, cy, cz, r; float ex, ey, ez; uint32_t flags; float nx, ny, nz, pad; };
+struct __align__(16) SphereDev { float cx, cy, cz, r; float ex, ey, ez; uint32_t flags; float nx, ny, nz, pad; };
 
 // ---- Philox4x32-10, key (seed_lo, seed_hi), counter (pixel_lo, pixel_hi, sample, block) ------------
 __host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
