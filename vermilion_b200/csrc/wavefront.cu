@@ -137,8 +137,8 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
                 sxy = rp.per ? ((sample / rp.per) & 3u) : 0u; // sampleX = bit 1, sampleY = bit 0 (loop nesting of pathtracer.cpp:242-247)
             }
         }
-        // every slot of the round gets a defined state, live or not
-        meta[idx] = 0u; // radiance[idx] is first written by the path's first k_shade iteration; throughput = (1,1,1,1) until a textured bounce writes it (kThrWritten)
+        // the path's meta word (depth, segments, kThrWritten) travels in the w of the ray's second float4 and starts at 0; radiance[idx] is
+        // first written by the path's first k_shade iteration; throughput = (1,1,1,1) until a textured bounce writes it
     }
     V3 o(0, 0, 0), d(0, 0, 0);
     if (live) {
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
         const uint64_t i = base + lane;
         bool alive = false;
         V3 nStart(0, 0, 0), nDir(0, 0, 0);
-        uint32_t slot = 0;
+        uint32_t slot = 0, mt_out = 0;
         if (i < n) {
             const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
             const float2 hr = __ldg(&hits[i]);
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             // Path state traffic: the throughput stays exactly (1,1,1,1) until a textured diffuse bounce scales it, and the radiance only
             // changes on an emitter hit or at the first hit — so thr[] is not touched while kThrWritten is clear, and radiance[] is only
             // read-modified-written when the sum can change (x + 1*0 = x; with a written throughput it may be non-finite, so always then).
-            uint32_t mt = meta[slot];
+            const uint32_t mt = __float_as_uint(rb.w); // path meta rides in the ray record: no dependent gather, no scatter per bounce
             uint32_t depth = mt & 0x7FFFu, segs = mt >> 16;
             const bool thr_written = (mt & kThrWritten) != 0u;
             float4 tp = thr_written ? thr[slot] : make_float4(1.f, 1.f, 1.f, 1.f);
@@ -307,7 +307,8 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                 }
             }
             if (thr_dirty) thr[slot] = tp;
-            meta[slot] = (depth & 0x7FFFu) | ((thr_written || thr_dirty) ? kThrWritten : 0u) | (segs << 16);
+            mt_out = (depth & 0x7FFFu) | ((thr_written || thr_dirty) ? kThrWritten : 0u) | (segs << 16);
+            if (!alive && radiance_query) meta[slot] = mt_out; // vmn_radiance reports the segments of each finished path
         }
         const uint32_t ballot = __ballot_sync(0xffffffffu, alive);
         if (ballot) {
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             if (alive) {
                 const uint32_t q = qb + __popc(ballot & ((1u << lane) - 1u));
                 rays_out[2ull * q] = make_float4(nStart.x, nStart.y, nStart.z, __uint_as_float(slot));
-                rays_out[2ull * q + 1] = make_float4(nDir.x, nDir.y, nDir.z, 0.f);
+                rays_out[2ull * q + 1] = make_float4(nDir.x, nDir.y, nDir.z, __uint_as_float(mt_out));
             }
         }
     }
@@ -840,7 +841,7 @@ __global__ void __launch_bounds__(kWfBlock) k_bf_shade1(SceneDev sc, const Spher
         const uint64_t i = base + lane;
         bool emit = false;
         V3 P(0, 0, 0), sdir(0, 0, 0), ldir(0, 0, 0);
-        uint32_t slot = 0;
+        uint32_t slot = 0, mt_out = 0;
         if (i < n) {
             const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
             const float2 hr = __ldg(&hits[i]);
