@@ -215,7 +215,7 @@ __device__ __forceinline__ V3 diffuse_dir(V3 N, V3 rDir, float c1, float s1, flo
 
 // One iteration of Radiance()'s loop (pathtracer.cpp:36-196) for every queued ray.
 #ifndef VMN_SHADE_MINB
-#define VMN_SHADE_MINB 8
+#define VMN_SHADE_MINB 9 // 56 registers: nine 128-thread CTAs per SM (8 -> 9: shade -1.3 %; 10 spills)
 #endif
 __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, RoundParams rp,
                                                     const float4* __restrict__ rays, const float2* __restrict__ hits,
@@ -518,7 +518,7 @@ static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const Roun
     vmn_status s = launch_extend(c, p, cur, it, clk, grid_extend);
     if (s != VMN_OK) return s;
     if (clk) clk->begin(ST_SHADE);
-    k_shade<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
+    k_shade<<<c->sm_count * VMN_SHADE_MINB, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
                                                          qc + cur, p->ray[cur ^ 1].as<float4>(), qc + (cur ^ 1), p->radiance.as<float4>(),
                                                          p->thr.as<float4>(), p->meta.as<uint32_t>(), radiance_query);
     if (clk) clk->end();
