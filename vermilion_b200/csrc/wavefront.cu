@@ -28,10 +28,13 @@ struct PixelMap {
 __device__ __forceinline__ bool map_pixel(const PixelMap& m, uint64_t lp, uint64_t* pixel) {
     if (m.tile == 0) { *pixel = m.begin + lp; return *pixel < (uint64_t)m.width * m.height; }
     const uint32_t tt = m.tile * m.tile;
-    const uint64_t j = lp / tt;
-    const uint32_t w = (uint32_t)(lp % tt);
+    uint64_t j; uint32_t w;
+    if ((lp >> 32) == 0) { const uint32_t j32 = (uint32_t)lp / tt; j = j32; w = (uint32_t)lp - j32 * tt; } // the usual case: 32-bit divides
+    else { j = lp / tt; w = (uint32_t)(lp % tt); }
     const uint64_t t = j * m.world + m.rank;
-    const uint32_t ty = (uint32_t)(t / m.tiles_x), tx = (uint32_t)(t % m.tiles_x);
+    uint32_t ty, tx;
+    if ((t >> 32) == 0) { ty = (uint32_t)t / m.tiles_x; tx = (uint32_t)t - ty * m.tiles_x; }
+    else { ty = (uint32_t)(t / m.tiles_x); tx = (uint32_t)(t % m.tiles_x); }
     const uint32_t x = tx * m.tile + (w % m.tile), y = ty * m.tile + (w / m.tile);
     if (x >= m.width || y >= m.height) return false;
     *pixel = (uint64_t)y * m.width + x;
@@ -262,7 +265,13 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
                 // pixel/sample of this slot (Philox counter)
                 uint64_t pixel; uint32_t sample;
                 if (radiance_query) { pixel = slot; sample = 0; }
-                else { map_pixel(pm, rp.lp0 + (slot % rp.n_local), &pixel); sample = rp.s0 + (uint32_t)(slot / rp.n_local); }
+                else {
+                    // slot = k * n_local + lp with a 32-bit slot: one 32-bit divide (a 64-bit one was 4 % of this kernel's instructions)
+                    uint32_t k = 0, lp = slot;
+                    if ((rp.n_local >> 32) == 0) { k = slot / (uint32_t)rp.n_local; lp = slot - k * (uint32_t)rp.n_local; }
+                    map_pixel(pm, rp.lp0 + lp, &pixel);
+                    sample = rp.s0 + k;
+                }
                 // iteration `segs` of the path draws from Philox block `segs` (block 0 holds the two pixel jitters): one block per bounce,
                 // generated once by every lane that still needs numbers; at most four are used (roulette, mirror test, two angles)
                 BounceRng rng;
