@@ -2,15 +2,15 @@
 //
 // Replaces PathTracer::Render's pixel loop and Radiance() (reference core/integrators/pathtracer.cpp:
 // 21-198, 200-328). Stages are separate kernels connected by device-resident ray queues:
-//   k_raygen      one thread per (pixel, sample) of the round: camera ray (pathtracer.cpp:251-280), path state reset
+//   k_raygen      one thread per (pixel, sample) of the round: camera ray (pathtracer.cpp:251-280), meta word 0
 //   k_extend      persistent warps, BVH8 closest hit per queued ray -> (t, triangle id)      [the hot kernel]
 //   k_shade       the rest of MeshEngine::RayCast (normals, 8 spheres) + one Radiance iteration; survivors are
 //                 appended to the next queue with one atomicAdd per warp (ballot/popc compaction)
 //   k_accumulate  per pixel, adds the round's finished samples to the film in sample order (deterministic,
 //                 no float atomics); in COMPAT mode also runs the reference's adaptive early-out state machine
 //   k_resolve     film sums -> RGBAZ (pathtracer.cpp:318-323, camera.cpp:106-113)
-// Path state is SoA indexed by slot; queue entries carry the slot. Queue counters live in device memory, so a
-// FIXED-mode round needs no host synchronisation.
+// Path state (radiance, throughput) is SoA indexed by slot; queue entries carry the slot and the path's meta word (depth,
+// throughput-written bit, segments). Queue counters live in device memory, so a FIXED-mode round needs no host synchronisation.
 #include "engine.cuh"
 #include "traverse.cuh"
 
@@ -64,11 +64,11 @@ __device__ __forceinline__ void camera_ray(const CamDev& c, uint64_t p, uint32_t
 
 struct PathPool {
     uint64_t capacity = 0;
-    DevBuf ray[2];    // 32 B per entry: (o.xyz, slot) (d.xyz, 0)
+    DevBuf ray[2];    // 32 B per entry: (o.xyz, slot) (d.xyz, meta = depth 0..14 | throughput-written bit 15 | segments 16..31)
     DevBuf hit;       // float2 per queue entry: (t, original triangle id)
     DevBuf radiance;  // float4 per slot (rgb, first-hit distance / -100)
     DevBuf thr;       // float4 per slot
-    DevBuf meta;      // path tracer: uint32 per slot (depth 0..14 | throughput-written bit 15 | segments 16..31); BRUTEFORCE: uint2 per pixel
+    DevBuf meta;      // vmn_radiance: final meta word per slot (segments cast); BRUTEFORCE: uint2 per pixel (nTotalSamples, done)
     DevBuf ctl;       // uint32 counters: [0..1] queue counts, [8..] claim counters (unsigned long long)
     DevBuf cstate;    // COMPAT per-local-pixel stratum state
     DevBuf bf_last;   // BRUTEFORCE per-local-pixel lastSampleColour (float4)
