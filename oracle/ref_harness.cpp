@@ -12,10 +12,12 @@
  *  - OpenImageIO is absent from the image: oracle/stubs/OpenImageIO/imagebuf.h
  *    declares the five names meshEngine.cpp:76-88 / camera.cpp:178-188 use (image
  *    file I/O only, never on the measured path).
- *  - Assimp's library is not linked by default (its build needs cmake-generated
- *    headers): the four Assimp::Importer symbols MeshEngine references are
- *    provided by oracle/assimp_link_stubs.cpp, ReadFile() there returns null.
- *    Scenes are injected as hand-filled aiScene/aiMesh structs (the exact structs
+ *  - Assimp: the reference's vendored extern/assimp (4.1.0) is compiled from its own
+ *    sources by oracle/Makefile (Importer core + OBJ importer + the post-process
+ *    steps MeshEngine::load asks for; no cmake) and linked in, so
+ *    ref_scene_load_file goes through the real MeshEngine::load -> ReadFile ->
+ *    processScene (meshEngine.cpp:95-150). Procedural scenes are still injected
+ *    as hand-filled aiScene/aiMesh structs (the exact structs
  *    MeshEngine::processScene and createBVH walk, meshEngine.cpp:533-724).
  *  - `private` is re-declared public for meshEngine.h ONLY in this translation
  *    unit, to set MeshEngine::pScene and call processScene() without
@@ -91,7 +93,8 @@ struct ref_scene {
     // MeshEngine tier
     Vermilion::LogEngine* logger = nullptr;
     Vermilion::MeshEngine* mesh = nullptr;
-    aiScene* scene = nullptr; // hand-filled; owned here
+    aiScene* scene = nullptr; // hand-filled; owned here (null for a file-loaded scene: the Importer owns that one)
+    std::vector<float> dpos, dnrm, duv; // ref_scene_load_file: what createBVH's walk read, for ref_scene_dump_triangles
 };
 
 struct ref_camera_settings {
@@ -222,6 +225,49 @@ ref_scene* ref_scene_create(const float* pos, const float* nrm, const float* uv,
         if (!s->mesh->processScene()) { /* leaves sceneAccelerator null */ }
     }
     return s;
+}
+
+/* The real loading path: MeshEngine::load(fName) with the reference's own flags (meshEngine.cpp:95-125) through the
+ * vendored Assimp, then processScene -> createBVH. The harness-owned accelerator tier (tris / ids / bvh, used by
+ * ref_intersect for triangle ids) is rebuilt from MeshEngine::sceneMeshes in createBVH's order (meshEngine.cpp:660-717),
+ * which defines the canonical triangle ids. Returns null when load() fails. */
+ref_scene* ref_scene_load_file(const char* path) {
+    Quiet q;
+    ref_scene* s = new ref_scene();
+    s->logger = new Vermilion::LogEngine("/dev/null", Vermilion::VermiLogFile, Vermilion::VermiLogLevelNone);
+    s->mesh = new Vermilion::MeshEngine(s->logger);
+    std::string f(path);
+    if (!s->mesh->load(f)) { delete s->mesh; delete s->logger; delete s; return nullptr; }
+    for (aiMesh* mesh : s->mesh->sceneMeshes)
+        for (uint32_t i = 0; i < mesh->mNumFaces; ++i) {
+            glm::vec3 v[3], n[3]; glm::vec2 t[3] = {glm::vec2(0), glm::vec2(0), glm::vec2(0)};
+            for (int k = 0; k < 3; ++k) {
+                unsigned idx = mesh->mFaces[i].mIndices[k];
+                v[k] = glm::vec3(mesh->mVertices[idx].x, mesh->mVertices[idx].y, mesh->mVertices[idx].z);
+                n[k] = glm::vec3(mesh->mNormals[idx].x, mesh->mNormals[idx].y, mesh->mNormals[idx].z);
+                if (mesh->HasTextureCoords(0)) t[k] = glm::vec2(mesh->mTextureCoords[0][idx].x, mesh->mTextureCoords[0][idx].y);
+            }
+            Triangle* tr = new Triangle(v[0], v[1], v[2], n[0], n[1], n[2], t[0], t[1], t[2]);
+            s->ids[tr] = (uint32_t)s->tris.size();
+            s->tris.push_back(tr);
+            for (int k = 0; k < 3; ++k) {
+                s->dpos.insert(s->dpos.end(), {v[k].x, v[k].y, v[k].z});
+                s->dnrm.insert(s->dnrm.end(), {n[k].x, n[k].y, n[k].z});
+                s->duv.insert(s->duv.end(), {t[k].x, t[k].y});
+            }
+        }
+    if (!s->tris.empty()) s->bvh = new BVH(s->tris);
+    return s;
+}
+
+uint64_t ref_scene_triangle_count(const ref_scene* s) { return s ? s->tris.size() : 0; }
+uint32_t ref_scene_mesh_count(const ref_scene* s) { return s && s->mesh ? (uint32_t)s->mesh->sceneMeshes.size() : 0; }
+
+/* The canonical triangle arrays (9 / 9 / 6 floats per triangle) of a scene made by ref_scene_load_file */
+void ref_scene_dump_triangles(const ref_scene* s, float* pos, float* nrm, float* uv) {
+    if (pos) memcpy(pos, s->dpos.data(), sizeof(float) * s->dpos.size());
+    if (nrm) memcpy(nrm, s->dnrm.data(), sizeof(float) * s->dnrm.size());
+    if (uv) memcpy(uv, s->duv.data(), sizeof(float) * s->duv.size());
 }
 
 void ref_scene_destroy(ref_scene* s) {

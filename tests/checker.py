@@ -241,6 +241,13 @@ class Ref:
                                             C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
             L.ref_render_bruteforce.restype = C.c_double
             L.ref_render_bruteforce.argtypes = [C.c_void_p, C.POINTER(RefCameraSettings), C.c_uint64, C.c_void_p, C.c_int]
+            L.ref_scene_load_file.restype = C.c_void_p
+            L.ref_scene_load_file.argtypes = [C.c_char_p]
+            L.ref_scene_triangle_count.restype = C.c_uint64
+            L.ref_scene_triangle_count.argtypes = [C.c_void_p]
+            L.ref_scene_mesh_count.restype = C.c_uint32
+            L.ref_scene_mesh_count.argtypes = [C.c_void_p]
+            L.ref_scene_dump_triangles.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
             L.ref_build_flags.restype = C.c_char_p
             L.ref_max_threads.restype = C.c_int
             cls._libs[variant] = L
@@ -253,8 +260,23 @@ class Ref:
         self.uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 6)
         self.h = self.L.ref_scene_create(_p(self.pos), _p(self.nrm), _p(self.uv), len(self.pos), int(mesh_engine))
 
+    @classmethod
+    def load_file(cls, path, variant="ieee"):
+        """The reference's own loading path: MeshEngine::load (its flags, meshEngine.cpp:103-125) through the vendored Assimp.
+        pos / nrm / uv are what MeshEngine::createBVH's walk read (meshEngine.cpp:660-717) — the canonical triangle order."""
+        self = cls.__new__(cls)
+        self.L = cls.lib(variant)
+        self.h = self.L.ref_scene_load_file(os.fsencode(path))
+        if not self.h:
+            raise RuntimeError(f"MeshEngine::load({path}) failed")
+        n = self.L.ref_scene_triangle_count(self.h)
+        self.n_meshes = self.L.ref_scene_mesh_count(self.h)
+        self.pos, self.nrm, self.uv = np.empty((n, 9), np.float32), np.empty((n, 9), np.float32), np.empty((n, 6), np.float32)
+        self.L.ref_scene_dump_triangles(self.h, _p(self.pos), _p(self.nrm), _p(self.uv))
+        return self
+
     def close(self):
-        if self.h:
+        if getattr(self, "h", None):
             self.L.ref_scene_destroy(self.h)
             self.h = None
 
