@@ -317,6 +317,17 @@ def main():
                 "note": "algorithmic bytes (SURVEY 8d B_ray); on C2 the ~60 MB of nodes+triangles stay L2-resident, so measured DRAM traffic is far below "
                         "the algorithmic bytes and the kernel is issue-bound (profiles/); tools/microbench_c3.py is the HBM-bound row"}
 
+    # the scene is L2-resident on C2: the L2's read bandwidth, measured with the traversal's own access width over a 48 MiB working
+    # set (vmn_probe_read_bandwidth), is the ceiling the algorithmic bytes actually run against; the same probe over 4 GiB reads HBM
+    try:
+        l2_gbs = eng.probe_read_bandwidth(48 << 20, 200)
+        hbm_read_gbs = eng.probe_read_bandwidth(4 << 30, 2)
+        roofline["l2"] = {"peak": l2_gbs, "unit": "GB/s", "achieved": achieved, "frac": achieved / l2_gbs, "hbm_read_probe": hbm_read_gbs,
+                          "how": "vmn_probe_read_bandwidth: LDG.128 (.cg) reads, 148 x 8 CTAs x 256 threads, 8 loads in flight per thread; "
+                                 "48 MiB working set x 200 passes (L2-resident), 4 GiB x 2 passes (HBM)"}
+    except Exception as e:
+        roofline["l2"] = {"peak": None, "error": repr(e)}
+
     cpu = None
     if not args.no_cpu and world == 1:
         try:

@@ -199,6 +199,12 @@ vmn_status vmn_read_image_rgba8(vmn_ctx* ctx, uint8_t* rgba8, float* depth);
 
 vmn_status vmn_get_stats(vmn_ctx* ctx, vmn_stats* out);
 
+/* Diagnostic for the traversal roofline (no counterpart in the reference): streams a zero-filled device buffer of
+ * `bytes` (>= 1 MiB) `passes` times with the 128-bit loads the traversal kernels use (L2-cached only) and returns the read
+ * bandwidth in GB/s. A working set well below the L2 size (126 MB) measures L2 read bandwidth — what bounds k_extend on a scene
+ * that stays L2-resident (C2) —, one well above it HBM read bandwidth. Not on the render path. */
+vmn_status vmn_probe_read_bandwidth(vmn_ctx* ctx, uint64_t bytes, uint32_t passes, double* gb_per_s);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -310,3 +310,15 @@ def test_top_level_sah_rebuild_keeps_hits(monkeypatch):
         c = common.classify_hits(e.intersect(rays), ref)
     assert c["bad"] == 0 and c["tie"] + c["edge"] <= 2e-4 * len(rays), c
     assert c["t_exact"] == c["hits"] and c["uv_err_max"] == 0.0, c
+
+
+@pytest.mark.gpu
+def test_read_bandwidth_probe_separates_l2_from_hbm():
+    """vmn_probe_read_bandwidth (the L2 ceiling bench.py reports beside the HBM roofline): a 32 MiB working set is served by the
+    L2 and must read faster than a 2 GiB one, which must itself reach a sane fraction of HBM bandwidth; bad arguments are refused."""
+    with engine.Engine(device=0) as eng:
+        l2 = eng.probe_read_bandwidth(32 << 20, 100)
+        hbm = eng.probe_read_bandwidth(2 << 30, 2)
+        assert l2 > hbm > 2000.0, (l2, hbm)
+        with pytest.raises(Exception):
+            eng.probe_read_bandwidth(1024, 1)

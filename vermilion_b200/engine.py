@@ -31,7 +31,8 @@ EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vm
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
            "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
-           "vmn_film_resolve_device", "vmn_film_upload", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats"]
+           "vmn_film_resolve_device", "vmn_film_upload", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats",
+           "vmn_probe_read_bandwidth"]
 
 
 class Config(C.Structure):
@@ -121,6 +122,7 @@ def load_library():
     L.vmn_film_aux_device.argtypes = [vp, C.POINTER(vp), C.POINTER(u64)]
     L.vmn_read_image_rgba8.argtypes = [vp, vp, vp]
     L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.vmn_probe_read_bandwidth.argtypes = [vp, u64, u32, C.POINTER(C.c_double)]
     _LIB = L
     return L
 
@@ -288,6 +290,12 @@ class Engine:
 
     def synchronize(self):
         self._chk(self.L.vmn_synchronize(self.h), "vmn_synchronize")
+
+    def probe_read_bandwidth(self, nbytes, passes):
+        """GB/s of 128-bit reads over a working set of nbytes (vmn_probe_read_bandwidth): L2 when it fits the L2, else HBM."""
+        g = C.c_double()
+        self._chk(self.L.vmn_probe_read_bandwidth(self.h, C.c_uint64(nbytes), C.c_uint32(passes), C.byref(g)), "vmn_probe_read_bandwidth")
+        return g.value
 
     def stats(self):
         s = Stats()
