@@ -322,3 +322,33 @@ def test_read_bandwidth_probe_separates_l2_from_hbm():
         assert l2 > hbm > 2000.0, (l2, hbm)
         with pytest.raises(Exception):
             eng.probe_read_bandwidth(1024, 1)
+
+
+@pytest.mark.parametrize("flags", [0, engine.ISECT_BVH2])
+def test_signed_zero_direction_components_match_oracle(eng, flags):
+    """Axis-parallel rays whose zero components carry either sign. The reference's inv_d is +-inf there (Ray.h:8) and its slab test
+    passes for an origin inside the slab whatever the sign of the zero (bbox.cpp:70-83); the wide traversal picks the near plane from
+    the direction's sign bit, which must agree with the sign of the clamped reciprocal it multiplies with."""
+    pos, nrm, uv = scene_spheres()
+    eng.set_scene(pos, nrm, uv)
+    rng = np.random.default_rng(17)
+    n = 60_000
+    tri = np.asarray(pos, np.float32).reshape(-1, 3, 3)
+    tgt = tri[rng.integers(0, len(tri), n)].mean(1)
+    axis = rng.integers(0, 3, n)
+    sign = rng.choice(np.array([-1.0, 1.0], np.float32), n)
+    d = np.zeros((n, 3), np.float32)
+    d[np.arange(n), axis] = sign
+    zero_sign = rng.choice(np.array([-0.0, 0.0], np.float32), (n, 3))
+    d = np.where(d == 0, zero_sign, d).astype(np.float32)
+    o = tgt.copy()
+    o[np.arange(n), axis] -= sign * np.float32(700.0)
+    rays = checker.make_rays(o.astype(np.float32), d)
+    assert np.signbit(rays["d"]).any() and (rays["d"] == 0).any()
+    got = eng.intersect(rays, flags)
+    ref = checker.Oracle(pos, nrm, uv).intersect(rays)
+    c = common.classify_hits(got, ref)
+    print(flags, c)
+    assert c["bad"] == 0, c
+    assert c["tie"] + c["edge"] <= 0.01 * n, c  # rays through triangle centroids of a closed mesh rarely graze an edge
+    assert c["hits"] > 0.9 * n and c["t_exact"] == c["hits"], c

@@ -19,7 +19,10 @@ namespace vmn {
 #define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
 #define VMN_LOCAL_STACK 52     // overflow entries in local memory
 #ifndef VMN_HIT8
-#define VMN_HIT8 1 // +2.7 % on k_extend (C2)
+#define VMN_HIT8 2 // 1: one hit bit per child, expanded once per node (+2.7 % on k_extend, C2); 2: the bits come from the sign of tf - tn
+#endif
+#ifndef VMN_SIGNED_LOADS
+#define VMN_SIGNED_LOADS 0 // 1: near / far plane words fetched from sign-dependent addresses (six LDG.64) instead of three LDG.128 + 12 SEL: k_extend +2.7 % (profiles/r01aj_ab_nodetest.txt)
 #endif
 #ifndef VMN_PREFETCH
 #define VMN_PREFETCH 0
@@ -138,7 +141,9 @@ __device__ __forceinline__ uint32_t child_hit(uint32_t metaw, uint32_t nxw, uint
     const float tfz = __fmaf_rn(byte_to_unit<J>(fzw, one), az, fbz);
     const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
     const float tf = fminf(fminf(tfx, tfy), fminf(tfz, best_t));
-#if VMN_HIT8
+#if VMN_HIT8 == 2
+    return __float_as_uint(tf - tn); // sign bit set = miss (no NaNs here: safe_inv keeps every slab distance finite); see trav_node
+#elif VMN_HIT8
     return tn <= tf ? 1u : 0u; // trav_node expands the 8 hit bits once per node
 #endif
     if (tn <= tf) {
@@ -170,7 +175,24 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
         }
         const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
+#if VMN_SIGNED_LOADS
+        // The near plane of an axis is the low plane for a positive direction and the high plane for a negative one. Instead of loading
+        // all six plane groups and swapping them with 12 SELs (ALU pipe, the one k_extend saturates), each 8-byte group is fetched from
+        // the address the direction's SIGN BIT picks: x low / high at +32 / +56, y at +40 / +64, z at +48 / +72, so near = low + 24 * sign
+        // and far = high - 24 * sign. The sign comes from IMAD.HI and the address from IMAD.WIDE (FMA pipe). Using the sign bit rather
+        // than d < 0 also pairs -0.0 with the negative reciprocal safe_inv gives it.
+        const uint4 q0 = __ldg(np), q1 = __ldg(np + 1);
+        const char* nb = reinterpret_cast<const char*>(np);
+        const uint32_t sgx = __umulhi(__float_as_uint(s.d.x), 2u), sgy = __umulhi(__float_as_uint(s.d.y), 2u), sgz = __umulhi(__float_as_uint(s.d.z), 2u);
+        const uint2 pnx = __ldg(reinterpret_cast<const uint2*>(nb + 32 + (uint64_t)sgx * 24u));
+        const uint2 pny = __ldg(reinterpret_cast<const uint2*>(nb + 40 + (uint64_t)sgy * 24u));
+        const uint2 pnz = __ldg(reinterpret_cast<const uint2*>(nb + 48 + (uint64_t)sgz * 24u));
+        const uint2 pfx = __ldg(reinterpret_cast<const uint2*>(nb + 56 + (int64_t)(int32_t)sgx * -24));
+        const uint2 pfy = __ldg(reinterpret_cast<const uint2*>(nb + 64 + (int64_t)(int32_t)sgy * -24));
+        const uint2 pfz = __ldg(reinterpret_cast<const uint2*>(nb + 72 + (int64_t)(int32_t)sgz * -24));
+#else
         const uint4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
+#endif
         if (COUNT) ++cnt->nodes;
         // per-axis: t(q) = q * a + b with a = 2^(e-127) / d, b = (p - o) / d, evaluated as fma(1 + q*2^-15, A, B), A = a * 2^15,
         // B = b - A, widened by |a| * 2^-8 (see byte_to_unit)
@@ -184,20 +206,39 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
         const float mx = fabsf(ax) * 0.00390625f, my = fabsf(ay) * 0.00390625f, mz = fabsf(az) * 0.00390625f;
         const float nbx = bx - mx, nby = by - my, nbz = bz - mz, fbx = bx + mx, fby = by + my, fbz = bz + mz;
         // near/far byte planes per axis (two words = 8 children each)
-        const bool ngx = s.d.x < 0.f, ngy = s.d.y < 0.f, ngz = s.d.z < 0.f;
+#if VMN_SIGNED_LOADS
+        const uint32_t nx0 = pnx.x, nx1 = pnx.y, fx0 = pfx.x, fx1 = pfx.y;
+        const uint32_t ny0 = pny.x, ny1 = pny.y, fy0 = pfy.x, fy1 = pfy.y;
+        const uint32_t nz0 = pnz.x, nz1 = pnz.y, fz0 = pfz.x, fz1 = pfz.y;
+#else
+        // the SIGN BIT, not d < 0: safe_inv gives -0.0 a negative reciprocal, so its near plane is the high one (with d < 0 such a ray
+        // missed every box: tests/test_gpu_parity.py::test_signed_zero_direction_components_match_oracle)
+        const bool ngx = __float_as_int(s.d.x) < 0, ngy = __float_as_int(s.d.y) < 0, ngz = __float_as_int(s.d.z) < 0;
         const uint32_t nx0 = ngx ? q3.z : q2.x, nx1 = ngx ? q3.w : q2.y, fx0 = ngx ? q2.x : q3.z, fx1 = ngx ? q2.y : q3.w;
         const uint32_t ny0 = ngy ? q4.x : q2.z, ny1 = ngy ? q4.y : q2.w, fy0 = ngy ? q2.z : q4.x, fy1 = ngy ? q2.w : q4.y;
         const uint32_t nz0 = ngz ? q4.z : q3.x, nz1 = ngz ? q4.w : q3.y, fz0 = ngz ? q3.x : q4.z, fz1 = ngz ? q3.y : q4.w;
+#endif
         uint32_t hitmask = 0;
         const uint32_t one = opaque_one(sc);
 #if VMN_HIT8
         // one hit bit per child slot, then a single expansion per node: internal hits are moved to the octant-ordered positions
         // 24 + (slot ^ oct_inv) by three conditional bit swaps; leaf hits OR in their unary triangle masks (usually 0-2 leaves)
+#if VMN_HIT8 == 2
+        // the hit test tn <= tf is the sign of tf - tn (FADD, FMA pipe); the eight signs are shifted into one register by funnel shifts,
+        // child 7 first so that child j lands on bit j: 8 FADD + 8 SHF instead of 8 FSETP + 8 SEL + 4 IADD3 on the ALU pipe
+        uint32_t miss8 = 0;
+#define VMN_CH(J, MW, S) miss8 = __funnelshift_l(child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv, one), miss8, 1)
+        VMN_CH(3, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(0, q1.w, 1);
+        VMN_CH(3, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(0, q1.z, 0);
+#undef VMN_CH
+        const uint32_t hit8 = ~miss8 & 0xFFu;
+#else
         uint32_t hit8 = 0;
 #define VMN_CH(J, MW, S) hit8 |= child_hit<J>(MW, nx##S, ny##S, nz##S, fx##S, fy##S, fz##S, Ax, Ay, Az, nbx, nby, nbz, fbx, fby, fbz, s.best_t, s.oct_inv, one) << (4 * S + J)
         VMN_CH(0, q1.z, 0); VMN_CH(1, q1.z, 0); VMN_CH(2, q1.z, 0); VMN_CH(3, q1.z, 0);
         VMN_CH(0, q1.w, 1); VMN_CH(1, q1.w, 1); VMN_CH(2, q1.w, 1); VMN_CH(3, q1.w, 1);
 #undef VMN_CH
+#endif
         {
             const uint32_t imask = q0.w >> 24;
             uint32_t x = hit8 & imask;
