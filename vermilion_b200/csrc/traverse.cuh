@@ -16,7 +16,9 @@
 namespace vmn {
 
 #define VMN_T_MISS 999999999.f // bvh.cpp:48
+#ifndef VMN_SH_STACK
 #define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
+#endif
 #define VMN_LOCAL_STACK 52     // overflow entries in local memory
 #ifndef VMN_HIT8
 #define VMN_HIT8 2 // 1: one hit bit per child, expanded once per node (+2.7 % on k_extend, C2); 2: the bits come from the sign of tf - tn

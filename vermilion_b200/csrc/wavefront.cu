@@ -11,6 +11,7 @@
 //   k_resolve     film sums -> RGBAZ (pathtracer.cpp:318-323, camera.cpp:106-113)
 // Path state (radiance, throughput) is SoA indexed by slot; queue entries carry the slot and the path's meta word (depth,
 // throughput-written bit, segments). Queue counters live in device memory, so a FIXED-mode round needs no host synchronisation.
+#include <cstdlib>
 #include "engine.cuh"
 #include "traverse.cuh"
 
@@ -491,6 +492,12 @@ enum { ST_RAYGEN = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_RESOLVE = 3 };
 
 static int extend_grid(vmn_ctx* c, bool count) {
     int per_sm = 0;
+    // experiment knob: VMN_CARVEOUT=<percent of the unified L1/shared array given to shared memory> for k_extend (default: driver's choice)
+    static const int carve = [] { const char* e = getenv("VMN_CARVEOUT"); return e ? atoi(e) : -1; }();
+    if (carve >= 0) {
+        cudaFuncSetAttribute(k_extend<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        cudaFuncSetAttribute(k_extend<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    }
     cudaError_t e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend<true>, kWfBlock, 0)
                           : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend<false>, kWfBlock, 0);
     if (e != cudaSuccess || per_sm < 1) per_sm = 4;
