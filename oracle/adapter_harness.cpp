@@ -61,3 +61,32 @@ extern "C" int adapter_render(ref_scene* scene, const ref_camera_settings* s, in
     delete cam;
     return rc;
 }
+
+/* Several cameras in one Render call (pathtracer.cpp:210 loops over cameraList): RGBAZ films, images[i] receives camera i's. */
+extern "C" int adapter_render_cameras(ref_scene* scene, const ref_camera_settings* s, int ncam, int mode, uint64_t seed, float** images,
+                                      char* err, int errlen) {
+    std::vector<Vermilion::Camera*> cams;
+    for (int i = 0; i < ncam; ++i) {
+        Vermilion::cameraSettings vcs;
+        vcs.imageResX = s[i].width; vcs.imageResY = s[i].height;
+        vcs.position = Vermilion::float3(s[i].position[0], s[i].position[1], s[i].position[2]);
+        vcs.rotation = Vermilion::float3(s[i].rotation_deg[0], s[i].rotation_deg[1], s[i].rotation_deg[2]);
+        vcs.fBackDistance = s[i].back_distance; vcs.horAngleOfView = 90.f; vcs.raysPerPixel = s[i].rays_per_pixel;
+        vcs.fBackSizeX = s[i].back_size_x; vcs.fBackSizeY = s[i].back_size_y; vcs.rayMaxBounces = 5; vcs.tileSize = 16;
+        vcs.renderMode = Vermilion::vermRenderMode::RGBAZ;
+        cams.push_back(new Vermilion::Camera(vcs));
+    }
+    Vermilion::B200Options opt;
+    opt.mode = mode; opt.seed = seed;
+    Vermilion::B200PathTracer* b200 = new Vermilion::B200PathTracer(opt);
+    Vermilion::Integrator* integrator = b200;
+    integrator->Render(cams, static_cast<Vermilion::MeshEngine*>(ref_scene_mesh_engine(scene)));
+    int rc = b200->ok() ? 0 : 1;
+    if (err && errlen > 0) { strncpy(err, b200->lastError().c_str(), errlen - 1); err[errlen - 1] = 0; }
+    for (int i = 0; i < ncam; ++i) {
+        if (rc == 0) memcpy(images[i], cams[i]->mImage, sizeof(float) * 5 * (size_t)cams[i]->RenderTargetSize);
+        delete cams[i];
+    }
+    delete integrator;
+    return rc;
+}

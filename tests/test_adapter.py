@@ -12,14 +12,14 @@ from vermilion_b200 import scenes
 
 ADAPTER = os.path.join(checker.ORACLE_DIR, "_ref", "libvermadapter.so")
 needs_adapter = pytest.mark.skipif(not (os.path.exists(ADAPTER) and checker.Ref.available("ieee")), reason="oracle/_ref/libvermadapter.so not built")
-RGB, RGBA, RGBAZ = 0, 1, 2  # vermRenderMode (camera.h:21-30)
+RGB, RGBA, RGBAZ, DEPTH = 0, 1, 2, 3  # vermRenderMode (camera.h:21-30)
 
 
 def adapter_render(ref, cs, render_mode, mode, seed, max_segments=5):
     L = C.CDLL(ADAPTER)
     L.adapter_render.argtypes = [C.c_void_p, C.POINTER(checker.RefCameraSettings), C.c_int, C.c_int, C.c_uint64, C.c_uint32, C.c_void_p,
                                  C.POINTER(C.c_uint64), C.c_char_p, C.c_int]
-    per = {RGB: 3, RGBA: 4, RGBAZ: 5}[render_mode]
+    per = {RGB: 3, RGBA: 4, RGBAZ: 5, DEPTH: 1}[render_mode]
     img = np.zeros((cs.width * cs.height, per), np.float32)
     rays = C.c_uint64()
     err = C.create_string_buffer(512)
@@ -65,6 +65,8 @@ def test_adapter_matches_oracle_through_the_integrator_interface(mode):
     # other film layouts go through Camera::setPixelValue (camera.cpp:88-124)
     rc, rgb, _, err = adapter_render(ref, cs, RGB, mode, 11)
     assert rc == 0 and np.array_equal(rgb, img[:, :3])
+    rc, dep, _, err = adapter_render(ref, cs, DEPTH, mode, 11)  # the one-float-per-pixel film (camera.cpp:73-75, 114-116)
+    assert rc == 0 and np.array_equal(dep[:, 0], img[:, 4])
 
 
 @pytest.mark.gpu
@@ -127,3 +129,31 @@ def test_adapter_progressive_checkpoints_resume(tmp_path):
         assert film_io.checkpoint_info(path.decode()).spp_done == 16
     finally:
         L.adapter_set_checkpoint(None, 0)
+
+
+@pytest.mark.gpu
+@needs_adapter
+def test_adapter_renders_every_camera_of_the_list():
+    """Render takes a camera LIST (integrators.h:14, pathtracer.cpp:210): two cameras of different size and pose in one call, each
+    film identical to the one a single-camera call produces (the scene is uploaded and built once)."""
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    ref = checker.Ref(pos, nrm, uv)
+    cams = [checker.camera_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16),
+            checker.camera_settings(40, 56, (300, 400, 1700), (3, -8, 0), 6.0, (2.0, 2.8), 8)]
+    singles = []
+    for cs in cams:
+        rc, img, _, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 7)
+        assert rc == 0, err
+        singles.append(img)
+    L = C.CDLL(ADAPTER)
+    L.adapter_render_cameras.argtypes = [C.c_void_p, C.POINTER(checker.RefCameraSettings), C.c_int, C.c_int, C.c_uint64, C.POINTER(C.c_void_p),
+                                         C.c_char_p, C.c_int]
+    arr = (checker.RefCameraSettings * 2)(*cams)
+    outs = [np.zeros((cs.width * cs.height, 5), np.float32) for cs in cams]
+    ptrs = (C.c_void_p * 2)(*[o.ctypes.data for o in outs])
+    err = C.create_string_buffer(512)
+    rc = L.adapter_render_cameras(ref.h, arr, 2, checker.MODE_FIXED, 7, ptrs, err, 512)
+    assert rc == 0, err.value
+    for a, b in zip(outs, singles):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        assert a[:, :3].max() > 0
