@@ -39,6 +39,10 @@ namespace vmn {
 #define VMN_COOP_ATOMIC 1     // fold pooled triangle results with a shared 64-bit atomicMin per hit instead of a per-owner loop
 #endif
 #define VMN_WSCRATCH 96       // words of shared scratch per warp (trav_tris_coop)
+#ifndef VMN_TRI_DEFER
+#define VMN_TRI_DEFER 16      // > 0: run the pooled triangle phase only once this many (ray, triangle) pairs are pending in the warp (or no
+                              // lane can advance otherwise); lanes with untested triangles wait, so every ray's own sequence is unchanged
+#endif
 #ifndef VMN_COOP
 #define VMN_COOP 1            // warp-pooled triangle tests (trav_tris_coop); 0 = per-lane loop
 #endif
@@ -322,6 +326,10 @@ __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const Scene
     const uint32_t n = __popc(bits);
     const uint32_t total = __reduce_add_sync(FULL, n);
     if (total == 0u) return;
+#if VMN_TRI_DEFER
+    // postpone a thin pool while some active lane can still advance without it (warp-uniform decision)
+    if (total < (uint32_t)VMN_TRI_DEFER && __ballot_sync(FULL, active && n == 0u) != 0u) return;
+#endif
     uint32_t incl = n;
 #pragma unroll
     for (int dlt = 1; dlt < 32; dlt <<= 1) {
@@ -469,14 +477,18 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
             if (exhausted) break;
             continue;
         }
+#if VMN_TRI_DEFER && VMN_COOP
+        if (active && s.tg.y == 0u) trav_node<COUNT>(s, sc, sstack, sstride, lstack, cnt);
+#else
         if (active) trav_node<COUNT>(s, sc, sstack, sstride, lstack, cnt);
+#endif
 #if VMN_COOP
         __syncwarp();
         trav_tris_coop<COUNT>(s, active, sc, wscratch, cnt);
 #else
         if (active) trav_tris<COUNT>(s, sc, cnt);
 #endif
-        if (active && !trav_pop(s, sstack, sstride, lstack)) {
+        if (active && s.tg.y == 0u && !trav_pop(s, sstack, sstride, lstack)) {
             store(ray, s);
             active = false;
         }
