@@ -11,7 +11,8 @@
  * What is NOT the reference here and why:
  *  - OpenImageIO is absent from the image: oracle/stubs/OpenImageIO/imagebuf.h
  *    declares the five names meshEngine.cpp:76-88 / camera.cpp:178-188 use (image
- *    file I/O only, never on the measured path).
+ *    file I/O only, never on the measured path); its ImageInput reads PFM files,
+ *    so MeshEngine::bindTexture itself runs (ref_scene_bind_texture_file).
  *  - Assimp: the reference's vendored extern/assimp (4.1.0) is compiled from its own
  *    sources by oracle/Makefile (Importer core + OBJ importer + the post-process
  *    steps MeshEngine::load asks for; no cmake) and linked in, so
@@ -288,6 +289,12 @@ void ref_scene_set_texture(ref_scene* s, const float* data, uint32_t w, uint32_t
     float* copy = new float[(size_t)w * h * c];
     memcpy(copy, data, sizeof(float) * (size_t)w * h * c);
     s->mesh->boundTextures.emplace_back((uint16_t)w, (uint16_t)h, (uint16_t)c, copy);
+}
+
+/* The reference's own MeshEngine::bindTexture (meshEngine.cpp:74-93) on a file (PFM, see the OpenImageIO stand-in). 1 = bound. */
+int ref_scene_bind_texture_file(ref_scene* s, const char* path) {
+    std::string f(path);
+    return s && s->mesh && s->mesh->bindTexture(f) ? 1 : 0;
 }
 
 /* BVH::getIntersection + Triangle::getNormal(uv) over the harness-owned triangles */

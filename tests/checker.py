@@ -241,6 +241,7 @@ class Ref:
                                             C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
             L.ref_render_bruteforce.restype = C.c_double
             L.ref_render_bruteforce.argtypes = [C.c_void_p, C.POINTER(RefCameraSettings), C.c_uint64, C.c_void_p, C.c_int]
+            L.ref_scene_bind_texture_file.argtypes = [C.c_void_p, C.c_char_p]
             L.ref_scene_load_file.restype = C.c_void_p
             L.ref_scene_load_file.argtypes = [C.c_char_p]
             L.ref_scene_triangle_count.restype = C.c_uint64
@@ -286,6 +287,10 @@ class Ref:
         tex = np.ascontiguousarray(tex, np.float32)
         h, w, c = tex.shape
         self.L.ref_scene_set_texture(self.h, _p(tex), w, h, c)
+
+    def bind_texture_file(self, path):
+        """MeshEngine::bindTexture(path) — the reference's own loader (meshEngine.cpp:74-93); the oracle build reads PFM."""
+        return bool(self.L.ref_scene_bind_texture_file(self.h, os.fsencode(path)))
 
     def intersect(self, rays, threads=0):
         out = np.zeros(len(rays), HIT)
