@@ -93,3 +93,26 @@ def test_b200_renders_the_assimp_loaded_cornell_through_the_integrator_seam(tmp_
     assert np.array_equal(img[:, 3:], oimg[:, 3:])  # alpha and the samples-taken plane
     assert (img[:, :3].view(np.uint32) == oimg[:, :3].view(np.uint32)).all(1).mean() > 0.97
     assert abs(nrays - onrays) <= 0.002 * onrays
+
+
+@needs_ref
+@pytest.mark.parametrize("with_nrm,with_uv", [(False, False), (False, True), (True, False)])
+def test_obj_writer_face_forms_load(tmp_path, with_nrm, with_uv):
+    """The four OBJ corner forms (v, v/vt, v//vn, v/vt/vn): positions always survive bit for bit and in order; missing normals are
+    generated by aiProcess_GenSmoothNormals (unit length, smoothed across corners at the same position), missing uvs stay zero."""
+    pos, nrm, uv = scenes.spheres(1, 1, 1, 150.0)  # one 80-triangle icosphere
+    path = scenes.write_obj(str(tmp_path / "s.obj"), pos, nrm if with_nrm else None, uv if with_uv else None)
+    ref = checker.Ref.load_file(path)
+    assert np.array_equal(ref.pos, pos.reshape(-1, 9))
+    n = ref.nrm.reshape(-1, 3, 3)
+    assert np.allclose(np.linalg.norm(n, axis=2), 1.0, atol=1e-5)
+    if with_nrm:
+        assert np.array_equal(ref.nrm, nrm.reshape(-1, 9))
+    else:
+        # corners at the same position are smoothed together even though the OBJ shares no indices (the step welds by position):
+        # on an icosphere that is close to the radial direction the generator itself uses
+        assert ((n * nrm.reshape(-1, 3, 3)).sum(2) > 0.98).all()
+    if with_uv:
+        assert np.array_equal(ref.uv.reshape(-1, 3, 2)[:, :, 0], uv.reshape(-1, 3, 2)[:, :, 0])
+    else:
+        assert not ref.uv.any()
