@@ -170,6 +170,7 @@ def main():
     ap.add_argument("--res", default="1920x1080")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-c3", action="store_true", help="skip the roofline_c3 record (10 M-triangle soup, N = 1 only)")
     ap.add_argument("--max-paths", type=int, default=32 << 20, help="paths in flight (112 B each); larger batches amortise the tail of every persistent launch")
     args = ap.parse_args()
     width, height = (int(x) for x in args.res.lower().split("x"))
@@ -303,14 +304,20 @@ def main():
     peak, peak_src = peaks()
     achieved = (rays / max(1e-9, extend_ms / 1e3)) * b_ray / 1e9
     n_extend = args.steps * 5 * -(-(npix * args.spp) // (args.max_paths // npix * npix if args.max_paths >= npix else args.max_paths))
-    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per k_extend launch, from the committed ncu --set full capture
+    # dram__bytes_read.sum + dram__bytes_write.sum per k_extend launch, from the committed ncu --set full capture (tools/update_traffic.py);
+    # only valid for the kernel sources it was captured on: a stamp that does not match the sources of this build is refused
+    traffic, traffic_note = None, "no capture"
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f)["k_extend"]["dram_bytes_per_launch"]
-    except Exception:
-        pass
+            tr = json.load(f)["k_extend"]
+        if tr.get("source_hash") == engine.kernel_source_hash():
+            traffic, traffic_note = tr["dram_bytes_per_launch"], tr.get("source", "")
+        else:
+            traffic_note = f"stale capture refused: taken on sources {tr.get('source_hash')}, this build is {engine.kernel_source_hash()}"
+    except Exception as e:
+        traffic_note = f"no capture ({e!r})"
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": peak_src, "bytes_per_ray": b_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
+                "traffic_source": traffic_note, "peak_source": peak_src, "bytes_per_ray": b_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                 "node_bytes": cst["node_bytes"], "tri_bytes": cst["tri_bytes"], "extend_ms_per_step": extend_ms / args.steps,
                 "extend_share_of_step": extend_ms / ms if world == 1 else None, "extend_launches": int(n_extend),
                 "algorithmic_bytes_per_launch": b_ray * rays / max(1, n_extend),
@@ -328,6 +335,19 @@ def main():
     except Exception as e:
         roofline["l2"] = {"peak": None, "error": repr(e)}
 
+    # ---- C3, the traversal-roofline row of BASELINE.json (configs[2]): 16 M incoherent rays vs the 10 M-triangle soup — the scene that does
+    # NOT fit the L2, so this is where the HBM roofline binds (C2 above is L2-resident). N = 1 only; same record as tools/microbench_c3.py.
+    roofline_c3 = None
+    if world == 1 and not args.no_c3:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import microbench_c3
+            eng.close()  # free the C2 pool (3.6 GB) before the 10 M-triangle scene goes up
+            eng = None
+            roofline_c3 = microbench_c3.c3_record(stream, reps=5, check=0 if args.no_cpu else 200_000, device=local, flush=flush)
+        except Exception as e:
+            roofline_c3 = {"error": repr(e)}
+
     cpu = None
     if not args.no_cpu and world == 1:
         try:
@@ -341,8 +361,9 @@ def main():
                       "parallelism": f"sample-slice x{world} + NCCL all-reduce of the film" if world > 1 else "single GPU",
                       "l2": "256 MiB L2 flush between timed steps", "paths_in_flight": args.max_paths},
            "spp_per_s": paths_all / npix / (ms / 1e3), "rays_per_step": rays_all / args.steps, "bvh_build_ms": build_ms,
-           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
-    eng.close()
+           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_c3": roofline_c3, "cpu_baseline": cpu}
+    if eng is not None:
+        eng.close()
     if world > 1:
         dist.destroy_process_group()
     sys.stdout.flush()

@@ -32,14 +32,15 @@ extern "C" {
 #pragma GCC visibility push(default) /* the library is built -fvisibility=hidden; these are its only exports */
 #endif
 
-#define VMN_ABI_VERSION 1
+#define VMN_ABI_VERSION 2
 
 typedef enum {
     VMN_OK = 0,
     VMN_ERR_INVALID = 1, /* bad argument */
     VMN_ERR_CUDA = 2,    /* CUDA runtime / launch failure, or no device */
     VMN_ERR_OOM = 3,     /* device or host allocation failed */
-    VMN_ERR_STATE = 4    /* call order violated (e.g. render before commit) */
+    VMN_ERR_STATE = 4    /* call order violated (e.g. render before commit), or a device-side consistency check failed
+                          * (a traversal stack overflowed: the results of that call are unreliable) */
 } vmn_status;
 
 typedef struct vmn_ctx vmn_ctx;
@@ -130,6 +131,9 @@ typedef struct {
     uint64_t nodes_visited, tris_tested; /* only with VMN_CFG_COUNTERS */
     double extend_ms, shade_ms, raygen_ms, resolve_ms, total_ms; /* device time of the last render, per stage */
     uint64_t kernel_launches;         /* kernels launched by the last render / intersect call */
+    uint64_t wide_depth;              /* levels of the BVH8 built by the last vmn_scene_commit (<= 128, the traversal stack) */
+    uint64_t l2_persist_bytes;        /* bytes of nodes + leaf triangles under an L2 persisting access-policy window (0 = none: the
+                                       * arrays exceed the device's persisting carve-out, or VMN_L2_PERSIST=0) */
 } vmn_stats;
 
 /* lifetime (replaces `new PathTracer()` + RenderEngine::assignIntegrator, main.cpp:60-63) */

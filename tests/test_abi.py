@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for name in decl:
         assert hasattr(lib, name), f"{name} declared in include/vermilion_b200.h but not exported"
     assert sorted(engine.EXPORTS) == decl
-    assert lib.vmn_abi_version() == 1
+    assert lib.vmn_abi_version() == 2
 
 
 def test_no_other_symbols_leak():

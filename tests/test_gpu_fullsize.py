@@ -86,3 +86,95 @@ def test_c2_bruteforce_first_hit_depth_matches_intersect(c2):
     assert (img[:, :3] >= 0).all() and (img[:, :3] <= 1).all()
     e.render(mode=engine.MODE_BRUTEFORCE, seed=1)
     assert np.array_equal(e.read_image(), img)
+
+
+# ---- C3: the traversal-roofline configuration (BASELINE.json configs[2]) at its full 10 M-triangle size ---------------------------------
+@pytest.fixture(scope="module")
+def c3():
+    pos, _, _ = scenes.soup(10_000_000, seed=1234)
+    e = engine.Engine(device=0)
+    e.set_scene(pos, None, None, spheres=np.zeros(0, engine.SPHERE))
+    yield e, pos
+    e.close()
+
+
+def test_c3_soup_two_traversals_and_oracle_sample(c3):
+    """4 M of C3's uniform random rays against the 10 M-triangle soup: the compressed BVH8 and the independent binary-LBVH traversal return
+    the same closest hits (ids equal up to reported ties, t and barycentrics bit-identical), a 100 k-ray sample is bit-exact against the CPU
+    oracle's own tree (BVH::getIntersection, bvh.cpp:47-145), and no traversal stack overflowed at this depth."""
+    e, pos = c3
+    st = e.stats()
+    assert st["n_triangles"] == 10_000_000 and 1 <= st["wide_depth"] <= 128
+    rays = scenes.uniform_rays(4_000_000, seed=4321, lo=0.0, hi=1000.0)
+    a = e.intersect(rays)
+    b = e.intersect(rays, engine.ISECT_BVH2)
+    e.synchronize()  # raises VMN_ERR_STATE if a push was dropped
+    same = a["tri"] == b["tri"]
+    assert (~same).sum() <= 2e-5 * len(rays)
+    assert a[same].tobytes() == b[same].tobytes()
+    assert (a["tri"] != engine.MISS).mean() > 0.9
+    n = 100_000
+    ref = checker.Oracle(pos).intersect(rays[:n].view(checker.RAY).reshape(-1))
+    c = common.classify_hits(a[:n], ref)
+    assert c["bad"] == 0 and c["tie"] + c["edge"] <= 5, c
+    assert c["t_exact"] == c["hits"] and c["uv_err_max"] == 0.0, c
+
+
+# ---- the C4 city at a size the CPU oracle can check (16 x 16 blocks, ~3 M triangles; C4 itself is 64 x 64 blocks) -----------------------
+def test_city_two_traversals_oracle_sample_and_tile_render():
+    pos, nrm, uv = scenes.city(16, 16, 23, 2024)
+    assert len(pos) > 2_500_000
+    with engine.Engine(device=0, max_paths=4 << 20) as e:
+        e.set_scene(pos, nrm, uv)
+        assert 1 <= e.stats()["wide_depth"] <= 128
+        lo, hi = pos.reshape(-1, 3).min(0), pos.reshape(-1, 3).max(0)
+        box = (np.array([lo[0], 5.0, lo[2]], np.float32), np.array([hi[0], 990.0, hi[2]], np.float32))
+        rays = np.concatenate([common.aimed_rays(pos, 1_000_000, 7, origin_box=box), common.aimed_rays(pos, 1_000_000, 8, spread=0.2, origin_box=box)])
+        a = e.intersect(rays)
+        b = e.intersect(rays, engine.ISECT_BVH2)
+        e.synchronize()
+        same = a["tri"] == b["tri"]
+        # buildings are closed boxes with shared edges: equal-t hits on two faces are ties and may resolve differently in the two trees
+        diff = np.nonzero(~same)[0]
+        assert len(diff) <= 1e-3 * len(rays)
+        assert np.array_equal(a["t"][diff], b["t"][diff]) or np.allclose(a["t"][diff], b["t"][diff], rtol=4e-7)
+        assert a[same].tobytes() == b[same].tobytes()
+        sub = np.concatenate([rays[:50_000], rays[-50_000:]])
+        ref = checker.Oracle(pos, nrm, uv).intersect(sub)
+        c = common.classify_hits(np.concatenate([a[:50_000], a[-50_000:]]), ref)
+        assert c["bad"] == 0, c
+        assert c["t_exact"] == c["hits"] and c["uv_err_max"] == 0.0, c
+        # the C4 split on one device: four tile shares of a frame from the C4 camera sum to the full frame bit for bit
+        cam = engine.camera_from_settings(960, 540, (0.0, 900.0, 1950.0), (25.0, 0.0, 0.0), 6.0, (3.6, 3.6 * 540 / 960), 4)
+        e.set_camera(cam)
+        e.render(mode=engine.MODE_FIXED, seed=1)
+        full = e.read_image(engine.FILM_SUM)
+        acc = np.zeros_like(full)
+        for r in range(4):
+            e.render(mode=engine.MODE_FIXED, seed=1, tile_size=64, tile_rank=r, tile_world=4)
+            acc += e.read_image(engine.FILM_SUM)
+        assert np.array_equal(acc, full) and (full[:, 3] == 4).all()
+
+
+# ---- degenerate trees (ADVICE r1): coincident centroids and a long Morton chain ---------------------------------------------------------
+def test_degenerate_scene_deep_tree_matches_oracle_or_reports():
+    """1e5 identical triangles (equal Morton codes: the builder's index tie-break adds up to 32 levels) plus a chain of triangles whose
+    centroids halve towards a corner (one Morton prefix per level): the deepest tree the LBVH can make. The commit must either succeed
+    with a depth inside the traversal stack — and then every hit matches the oracle — or fail with VMN_ERR_STATE; never a silent miss."""
+    tri = np.array([[10, 10, 10, 12, 10, 10, 10, 12, 10]], np.float32)
+    chain = np.zeros((60, 9), np.float32)
+    for k in range(60):
+        c = 1000.0 * 2.0 ** (-k)
+        chain[k] = [c, c, c, c * 1.25, c, c, c, c * 1.25, c]
+    pos = np.concatenate([np.repeat(tri, 100_000, 0), chain])
+    rays = common.aimed_rays(pos, 4000, 5)
+    with engine.Engine(device=0) as e:
+        e.set_scene(pos, None, None, spheres=np.zeros(0, engine.SPHERE))
+        assert 1 <= e.stats()["wide_depth"] <= 128
+        for flags in (0, engine.ISECT_BVH2):
+            got = e.intersect(rays, flags)  # raises (VMN_ERR_STATE) if a traversal stack overflowed
+            ref = checker.Oracle(pos).intersect(rays)
+            c = common.classify_hits(got, ref)
+            assert c["bad"] == 0 and c["edge"] <= 2, c
+            hit = (got["tri"] != engine.MISS) & (ref["tri"] != checker.MISS)
+            assert np.array_equal(got["t"][hit], ref["t"][hit])  # identical triangles tie on t whichever id wins

@@ -35,6 +35,17 @@ vmn_status dev_alloc(vmn_ctx* c, DevBuf& b, size_t bytes) {
     return VMN_OK;
 }
 
+vmn_status check_device_error(vmn_ctx* c) {
+    if (!c->errflag.p) return VMN_OK;
+    uint32_t h = 0;
+    VMN_CUDA(c, cudaMemcpyAsync(&h, c->errflag.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (h == 0u) return VMN_OK;
+    VMN_CUDA(c, cudaMemsetAsync(c->errflag.p, 0, 4, c->stream));
+    return fail(c, VMN_ERR_STATE, "device error word 0x%x:%s the results of this call are unreliable", h,
+                (h & VMN_DEVERR_STACK) ? " a traversal stack overflowed (tree deeper than the stack);" : "");
+}
+
 vmn_status dev_reserve(vmn_ctx* c, DevBuf& b, size_t bytes) {
     if (b.bytes >= bytes && b.p) return VMN_OK;
     return dev_alloc(c, b, bytes);
@@ -69,6 +80,36 @@ void camera_matrix(const vmn_camera& cam, float m[16]) {
 
 using namespace vmn;
 
+// Keep the arrays every ray walks (leaf triangles + wide nodes, one allocation) in the L2 while the ray queues — gigabytes per frame,
+// each byte touched once — stream past them: a persisting access-policy window on the context's stream when the arrays fit the device's
+// persisting carve-out (C2: 75 MB of a 126 MB L2); scenes that do not fit (C3, C4) get no window. The queue traffic itself is issued with
+// evict-first loads / stores (VMN_STREAM_HINTS, traverse.cuh). Env VMN_L2_PERSIST=0 switches the window off (A/B).
+static void apply_l2_policy(vmn_ctx* c) {
+    static const int enabled = [] { const char* e = getenv("VMN_L2_PERSIST"); return e ? atoi(e) : 1; }();
+    int max_persist = 0, max_window = 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
+    cudaStreamAttrValue v{};
+    const bool want = enabled && c->trav_bytes > 0 && max_persist > 0 && c->trav_bytes <= (uint64_t)max_persist && c->trav_bytes <= (uint64_t)max_window;
+    if (want) {
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist);
+        v.accessPolicyWindow.base_ptr = c->tris.p;
+        v.accessPolicyWindow.num_bytes = (size_t)c->trav_bytes;
+        v.accessPolicyWindow.hitRatio = 1.0f;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        c->l2_window = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess;
+    } else if (c->l2_window) {
+        v.accessPolicyWindow.num_bytes = 0; // disables the window
+        cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v);
+        cudaCtxResetPersistingL2Cache();
+        c->l2_window = false;
+    }
+    cudaGetLastError();
+    c->stats.l2_persist_bytes = c->l2_window ? c->trav_bytes : 0;
+}
+
+
 #define CHECK_CTX(c) do { if (!(c)) return VMN_ERR_INVALID; } while (0)
 #define SET_DEVICE(c) VMN_CUDA(c, cudaSetDevice((c)->device))
 
@@ -97,6 +138,9 @@ vmn_status vmn_create(const vmn_config* cfg, vmn_ctx** out) {
     if (cfg && cfg->stream) { c->stream = (cudaStream_t)cfg->stream; c->own_stream = false; }
     else { VMN_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
     for (auto& ev : c->ev) VMN_CUDA(c, cudaEventCreate(&ev));
+    vmn_status s = dev_alloc(c, c->errflag, 4);
+    if (s != VMN_OK) return s;
+    VMN_CUDA(c, cudaMemsetAsync(c->errflag.p, 0, 4, c->stream));
     return VMN_OK;
 }
 
@@ -104,9 +148,10 @@ void vmn_destroy(vmn_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->l2_window) { c->trav_bytes = 0; apply_l2_policy(c); } // a borrowed stream must not keep a window over freed memory
     pool_destroy(c);
-    for (DevBuf* b : {&c->pos, &c->nrm, &c->uv, &c->tris, &c->tris_sorted, &c->tris_orig, &c->shade, &c->wide, &c->b_min, &c->b_max,
-                      &c->b_child, &c->spheres, &c->tex, &c->tex1, &c->film, &c->film_aux, &c->q_in, &c->q_out, &c->counters})
+    for (DevBuf* b : {&c->pos, &c->nrm, &c->uv, &c->tris, &c->tris_sorted, &c->tris_orig, &c->shade, &c->b_min, &c->b_max,
+                      &c->b_child, &c->spheres, &c->tex, &c->tex1, &c->film, &c->film_aux, &c->q_in, &c->q_out, &c->counters, &c->errflag})
         dev_free(*b);
     for (DevBuf& b : c->build_scratch) dev_free(b);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -120,18 +165,20 @@ vmn_status vmn_set_stream(vmn_ctx* c, void* s) {
     CHECK_CTX(c);
     SET_DEVICE(c);
     if (c->stream) VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint64_t tb = c->trav_bytes;
+    if (c->l2_window) { c->trav_bytes = 0; apply_l2_policy(c); c->trav_bytes = tb; }
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     c->own_stream = false;
     if (s) c->stream = (cudaStream_t)s;
     else { VMN_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
+    if (c->committed) apply_l2_policy(c);
     return VMN_OK;
 }
 
 vmn_status vmn_synchronize(vmn_ctx* c) {
     CHECK_CTX(c);
     SET_DEVICE(c);
-    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-    return VMN_OK;
+    return check_device_error(c); // synchronises; reports a traversal error raised by an earlier asynchronous (_device) call
 }
 
 static vmn_status upload(vmn_ctx* c, DevBuf& b, const void* src, size_t bytes) {
@@ -222,6 +269,7 @@ vmn_status vmn_scene_commit(vmn_ctx* c) {
     SET_DEVICE(c);
     vmn_status s = build_bvh(c);
     if (s != VMN_OK) return s;
+    apply_l2_policy(c);
     c->scene.n_spheres = c->n_spheres;
     scene_bind_textures(c);
     // the staged arrays stay allocated (reused by the next vmn_scene_set_triangles); they are 96 B/triangle
@@ -245,8 +293,7 @@ vmn_status stage_rays(vmn_ctx* c, const vmn_ray* rays, uint64_t n, size_t out_by
 }
 vmn_status fetch(vmn_ctx* c, void* dst, size_t bytes) {
     if (bytes) VMN_CUDA(c, cudaMemcpyAsync(dst, c->q_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
-    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-    return VMN_OK;
+    return check_device_error(c); // synchronises the stream
 }
 vmn_status read_counters(vmn_ctx* c) {
     if ((c->flags & VMN_CFG_COUNTERS) && c->counters.p) {
@@ -317,8 +364,7 @@ vmn_status vmn_radiance(vmn_ctx* c, const vmn_ray* rays, uint64_t n, uint64_t se
     if ((s = launch_radiance(c, c->q_in.as<vmn_ray>(), n, seed, mode, max_segments ? max_segments : 5, d_out, d_cnt)) != VMN_OK) return s;
     if (n) VMN_CUDA(c, cudaMemcpyAsync(out, d_out, 16 * n, cudaMemcpyDeviceToHost, c->stream));
     if (n && rays_cast) VMN_CUDA(c, cudaMemcpyAsync(rays_cast, d_cnt, 4 * n, cudaMemcpyDeviceToHost, c->stream));
-    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-    return VMN_OK;
+    return check_device_error(c); // synchronises the stream
 }
 
 // ---- camera, film, render -------------------------------------------------------------------------
@@ -373,9 +419,10 @@ vmn_status vmn_render(vmn_ctx* c, const vmn_render_params* p) {
     if (!c->have_cam) return fail(c, VMN_ERR_STATE, "no camera set");
     if (p->mode != VMN_MODE_COMPAT && p->mode != VMN_MODE_FIXED && p->mode != VMN_MODE_BRUTEFORCE) return fail(c, VMN_ERR_INVALID, "bad mode %d", p->mode);
     SET_DEVICE(c);
-    if (p->mode == VMN_MODE_BRUTEFORCE) return render_bruteforce(c, p);
-    c->film_bf = false;
-    return render_frame(c, p);
+    vmn_status s;
+    if (p->mode == VMN_MODE_BRUTEFORCE) s = render_bruteforce(c, p);
+    else { c->film_bf = false; s = render_frame(c, p); }
+    return s != VMN_OK ? s : check_device_error(c);
 }
 
 vmn_status vmn_film_device(vmn_ctx* c, float** d_sum, uint64_t* n_floats) {

@@ -526,8 +526,10 @@ vmn_status build_bvh(vmn_ctx* c) {
     const uint32_t n = (uint32_t)n64;
     cudaStream_t st = c->stream;
     c->scene = SceneDev{};
+    c->scene.err = c->errflag.as<uint32_t>();
     c->scene.n_tris = n;
     c->n_wide = 0;
+    c->trav_bytes = 0;
     c->stats.n_triangles = n; c->stats.n_nodes = 0; c->stats.n_wide_nodes = 0;
     c->stats.node_bytes = 80; c->stats.tri_bytes = 48; // payload bytes
     if (n == 0) return VMN_OK;
@@ -554,10 +556,12 @@ vmn_status build_bvh(vmn_ctx* c) {
     TRY(dev_alloc(c, c->b_min, 16ull * nnodes)); TRY(dev_alloc(c, c->b_max, 16ull * nnodes));
     TRY(dev_alloc(c, c->b_child, 8ull * n));
     TRY(dev_alloc(c, c->tris_sorted, sizeof(TriRec) * (uint64_t)n));
-    TRY(dev_alloc(c, c->tris, sizeof(LeafTri) * (uint64_t)n));
+    // the two arrays the traversal reads — leaf triangles, then the wide nodes — share one allocation, so that a single L2 access-policy
+    // window (api.cu: apply_l2_policy) can cover both: [tris: n records][nodes: capacity n, n_wide used]
+    TRY(dev_alloc(c, c->tris, (sizeof(LeafTri) + sizeof(WideNode)) * (uint64_t)n));
+    WideNode* const wide_nodes = reinterpret_cast<WideNode*>(c->tris.as<char>() + sizeof(LeafTri) * (uint64_t)n);
     TRY(dev_alloc(c, c->tris_orig, sizeof(TriRec) * (uint64_t)n));
     TRY(dev_alloc(c, c->shade, sizeof(ShadeRec) * (uint64_t)n));
-    TRY(dev_alloc(c, c->wide, sizeof(WideNode) * (uint64_t)n));
 
     const uint32_t B = 256;
     const float* pos = c->pos.as<float>();
@@ -588,12 +592,13 @@ vmn_status build_bvh(vmn_ctx* c) {
     uint2 root = make_uint2(0u, 0u); // binary node 0 is the root (for n == 1 it is the only leaf)
     TRYCUDA(cudaMemcpyAsync(qa.p, &root, sizeof(root), cudaMemcpyHostToDevice, st));
     TRYCUDA(cudaMemcpyAsync(ctl.p, &h, sizeof(h), cudaMemcpyHostToDevice, st));
-    uint32_t n_in = 1;
+    uint32_t n_in = 1, levels = 0;
     DevBuf* qi = &qa; DevBuf* qo = &qb;
     while (n_in) {
+        ++levels;
         k_collapse<<<cdiv(n_in, 128), 128, 0, st>>>(qi->as<uint2>(), n_in, qo->as<uint2>(), ctl.as<CollapseCtl>(), (int)n, c->b_child.as<int2>(),
                                                     first.as<int>(), count.as<uint32_t>(), c->b_min.as<float4>(), c->b_max.as<float4>(),
-                                                    c->tris_sorted.as<TriRec>(), c->wide.as<WideNode>(), c->tris.as<LeafTri>());
+                                                    c->tris_sorted.as<TriRec>(), wide_nodes, c->tris.as<LeafTri>());
         TRYCUDA(cudaMemcpyAsync(&h, ctl.p, sizeof(h), cudaMemcpyDeviceToHost, st));
         TRYCUDA(cudaStreamSynchronize(st));
         n_in = h.q_out;
@@ -602,6 +607,11 @@ vmn_status build_bvh(vmn_ctx* c) {
         std::swap(qi, qo);
     }
     if (h.n_tris != n) { cleanup(); return fail(c, VMN_ERR_STATE, "collapse placed %u of %u triangles", h.n_tris, n); }
+    // the BVH8 traversal keeps at most one stack entry per level: a tree deeper than the stack is refused here rather than traversed wrongly
+    // (VMN_DEBUG_NO_DEPTH_CHECK=1 lets a too-deep tree through: the test hook for the device-side overflow report)
+    static const bool skip_depth_check = [] { const char* e = getenv("VMN_DEBUG_NO_DEPTH_CHECK"); return e && e[0] == '1'; }();
+    if (levels > kTravStackCap && !skip_depth_check) { cleanup(); return fail(c, VMN_ERR_STATE, "BVH8 depth %u exceeds the traversal stack (%u entries)", levels, kTravStackCap); }
+    c->stats.wide_depth = levels;
     c->n_wide = h.n_nodes;
     VMN_CUDA(c, cudaEventRecord(c->ev[1], st));
     VMN_CUDA(c, cudaStreamSynchronize(st));
@@ -612,7 +622,8 @@ vmn_status build_bvh(vmn_ctx* c) {
 #undef dev_alloc
 #undef TRYCUDA
 
-    c->scene.nodes = c->wide.as<WideNode>();
+    c->scene.nodes = wide_nodes;
+    c->trav_bytes = sizeof(LeafTri) * (uint64_t)n + sizeof(WideNode) * (uint64_t)c->n_wide;
     c->scene.tris = c->tris.as<LeafTri>();
     c->scene.tris_sorted = c->tris_sorted.as<TriRec>();
     c->scene.tris_orig = c->tris_orig.as<TriRec>();

@@ -87,7 +87,16 @@ struct Bvh2 {
     uint32_t n_prims;
 };
 
+// Traversal stacks (BVH8: one entry per wide level with pending siblings; BVH2: one per binary level) hold this many entries;
+// build_bvh() measures the depth of both trees and refuses to commit one that could overflow them.
+#ifndef VMN_STACK_CAP
+#define VMN_STACK_CAP 128 // (the `tinystack` test variant of csrc/Makefile builds with 3 to reach the overflow paths)
+#endif
+constexpr uint32_t kTravStackCap = VMN_STACK_CAP;
+#define VMN_DEVERR_STACK 1u // device error word: a traversal push was dropped (result of that ray is unreliable)
+
 struct SceneDev {
+    uint32_t* err;           // device error word owned by the context (VMN_DEVERR_*), checked at every synchronising entry point
     const WideNode* nodes;   // BVH8
     const LeafTri* tris;     // in BVH8 leaf order
     const TriRec* tris_sorted; // in Morton order (BVH2 leaves)

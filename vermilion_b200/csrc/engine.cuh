@@ -36,7 +36,9 @@ struct vmn_ctx {
     bool committed = false;
 
     // built scene
-    vmn::DevBuf tris, tris_sorted, tris_orig, shade, wide, b_min, b_max, b_child;
+    vmn::DevBuf tris, tris_sorted, tris_orig, shade, b_min, b_max, b_child; // tris: leaf triangles + wide nodes (one allocation)
+    uint64_t trav_bytes = 0;   // bytes of `tris` the traversal reads (leaf triangles + the wide nodes in use)
+    bool l2_window = false;    // an L2 persisting access-policy window is set on `stream`
     vmn::DevBuf spheres, tex, tex1;
     vmn::DevBuf build_scratch[16]; // bvh_build.cu, grow-only
     uint32_t n_spheres = 0, tex_w = 0, tex_h = 0, tex_c = 0, tex1_w = 0, tex1_h = 0, tex1_c = 0;
@@ -59,6 +61,7 @@ struct vmn_ctx {
 
     // scratch for the ray-query entry points
     vmn::DevBuf q_in, q_out, counters;
+    vmn::DevBuf errflag;   // one uint32 of VMN_DEVERR_* bits set by kernels (SceneDev::err)
 
     vmn_stats stats{};
     cudaEvent_t ev[8] = {};
@@ -70,6 +73,7 @@ vmn_status fail(vmn_ctx* c, vmn_status s, const char* fmt, ...);
 vmn_status dev_alloc(vmn_ctx* c, DevBuf& b, size_t bytes);       // (re)allocate exactly
 vmn_status dev_reserve(vmn_ctx* c, DevBuf& b, size_t bytes);     // grow only
 void dev_free(DevBuf& b);
+vmn_status check_device_error(vmn_ctx* c); // synchronises the stream; VMN_ERR_STATE if a kernel raised a VMN_DEVERR_* bit (and clears it)
 
 #define VMN_CUDA(c, expr)                                                                                   \
     do {                                                                                                    \

@@ -25,7 +25,7 @@ __device__ __forceinline__ bool claim_rays(unsigned long long* next, uint64_t n,
 
 __device__ __forceinline__ void load_ray(const vmn_ray* __restrict__ rays, uint64_t i, V3* o, V3* d) {
     const float4* p = reinterpret_cast<const float4*>(rays + i);
-    const float4 a = __ldg(p), b = __ldg(p + 1);
+    const float4 a = ld_stream(p), b = ld_stream(p + 1);
     *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
 }
 
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(Scene
             const V3 hp = o + d * t; // bvh.cpp:140
             tri_bary(load_tri(sc.tris_orig + id), hp, &u, &v);
         }
-        reinterpret_cast<float4*>(out)[i] = make_float4(t, u, v, __uint_as_float(id));
+        st_stream(&reinterpret_cast<float4*>(out)[i], make_float4(t, u, v, __uint_as_float(id)));
     };
     if (WIDE) {
         persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kTraceBlock / 32)), refill_min, sstack, kTraceBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,

@@ -19,7 +19,9 @@ namespace vmn {
 #ifndef VMN_SH_STACK
 #define VMN_SH_STACK 12        // traversal stack entries per thread kept in shared memory
 #endif
-#define VMN_LOCAL_STACK 52     // overflow entries in local memory
+#ifndef VMN_LOCAL_STACK
+#define VMN_LOCAL_STACK (VMN_STACK_CAP - VMN_SH_STACK) // overflow entries in local memory: 128 in all (kTravStackCap, checked against the tree at commit)
+#endif
 #ifndef VMN_HIT8
 #define VMN_HIT8 2 // 1: one hit bit per child, expanded once per node (+2.7 % on k_extend, C2); 2: the bits come from the sign of tf - tn
 #endif
@@ -47,7 +49,30 @@ namespace vmn {
 #define VMN_COOP 1            // warp-pooled triangle tests (trav_tris_coop); 0 = per-lane loop
 #endif
 
+static_assert(VMN_SH_STACK + VMN_LOCAL_STACK == (int)kTravStackCap, "shared + local stack entries must add up to kTravStackCap");
+
 struct TravCounters { unsigned long long nodes, tris; };
+
+// Queue traffic (rays in, hits out, rays appended by the shading stage) is touched once per launch and is far larger than the L2: it is
+// issued with the evict-first cache operators (ld.global.cs / st.global.cs), so that it does not push the nodes and triangles every ray
+// re-reads out of the L2 (on C2, 1.07 GB of the 2.40 GB of DRAM traffic per k_extend launch was scene re-fetch, profiles/r01ak).
+#ifndef VMN_STREAM_HINTS
+#define VMN_STREAM_HINTS 1
+#endif
+template <class T> __device__ __forceinline__ T ld_stream(const T* p) {
+#if VMN_STREAM_HINTS
+    return __ldcs(p);
+#else
+    return __ldg(p);
+#endif
+}
+template <class T> __device__ __forceinline__ void st_stream(T* p, T v) {
+#if VMN_STREAM_HINTS
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
 
 // Triangle::getIntersection (triangle.cpp:4-54): Moeller-Trumbore, two-sided.
 __device__ __forceinline__ bool tri_intersect(const TriRec& T, V3 o, V3 d, float* t) {
@@ -175,10 +200,11 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
         const uint32_t rel = __popc(s.ng.y & 0xFFu & ((1u << slot) - 1u));
         const uint32_t nidx = s.ng.x + rel;
         if (s.ng.y & 0xFF000000u) { // siblings still pending
-            // one entry per level at most, so 64 entries cover any tree the builder makes (depth <= 63 Morton bits); the bound only
-            // keeps a corrupt tree from writing outside the array
+            // one entry per wide-tree level at most; vmn_scene_commit refuses a tree deeper than the stack (kTravStackCap), so the last
+            // branch is unreachable for a committed scene — if it ever runs, the dropped push is REPORTED (VMN_ERR_STATE), never silent
             if (s.sp < VMN_SH_STACK) { sstack[s.sp * sstride] = s.ng; ++s.sp; }
             else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
+            else atomicOr(sc.err, VMN_DEVERR_STACK);
         }
         const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
 #if VMN_SIGNED_LOADS
@@ -283,10 +309,8 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
 #endif
         }
 #endif
-    } else {
-        s.tg = s.ng;
-        s.ng = make_uint2(0u, 0u);
     }
+    // (no else: the stack only ever holds groups with pending hit bits, and trav_pop refills ng before the next call)
 }
 
 // per-lane triangle loop (single-ray form)
@@ -510,7 +534,7 @@ __device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, f
     if (n == 0 || ray_is_nan(o, d)) { *t_out = best_t; return best; }
     const int nint = (int)n - 1;
     const float idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
-    int stack[64];
+    int stack[kTravStackCap];
     int sp = 0;
     int node = 0;
     while (true) {
@@ -543,7 +567,8 @@ __device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, f
         if (hit[0] && hit[1]) {
             const bool swap = tn[1] < tn[0];
             const int nearc = swap ? c.y : c.x, farc = swap ? c.x : c.y;
-            if (sp < 64) stack[sp++] = farc;
+            if (sp < (int)kTravStackCap) stack[sp++] = farc;
+            else atomicOr(sc.err, VMN_DEVERR_STACK);
             node = nearc;
         } else if (hit[0]) node = c.x;
         else if (hit[1]) node = c.y;

@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
     base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
     if (live) {
         const uint32_t q = base + __popc(ballot & ((1u << lane) - 1u));
-        rays[2ull * q] = make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx));
-        rays[2ull * q + 1] = make_float4(d.x, d.y, d.z, 0.f);
+        st_stream(&rays[2ull * q], make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx)));
+        st_stream(&rays[2ull * q + 1], make_float4(d.x, d.y, d.z, 0.f));
     }
 }
 
@@ -180,11 +180,11 @@ __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev s
     TravCounters cnt{0ull, 0ull};
     persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) {
-                                const float4 a = __ldg(&rays[2 * i]), b = __ldg(&rays[2 * i + 1]);
+                                const float4 a = ld_stream(&rays[2 * i]), b = ld_stream(&rays[2 * i + 1]);
                                 *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
                             },
                             [&](uint64_t i, const Trav& s) {
-                                hits[i] = make_float2(s.best_t, __uint_as_float(leaf_original_id(sc.tris, s.best)));
+                                st_stream(&hits[i], make_float2(s.best_t, __uint_as_float(leaf_original_id(sc.tris, s.best))));
                             }, rays);
     if (COUNT) { atomicAdd(&gcnt->nodes, cnt.nodes); atomicAdd(&gcnt->tris, cnt.tris); }
 }
@@ -234,8 +234,8 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
         V3 nStart(0, 0, 0), nDir(0, 0, 0);
         uint32_t slot = 0, mt_out = 0;
         if (i < n) {
-            const float4 ra = __ldg(&rays[2 * i]), rb = __ldg(&rays[2 * i + 1]);
-            const float2 hr = __ldg(&hits[i]);
+            const float4 ra = ld_stream(&rays[2 * i]), rb = ld_stream(&rays[2 * i + 1]);
+            const float2 hr = ld_stream(&hits[i]);
             slot = __float_as_uint(ra.w);
             V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
             const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y));
@@ -328,8 +328,8 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             qb = __shfl_sync(0xffffffffu, qb, leader);
             if (alive) {
                 const uint32_t q = qb + __popc(ballot & ((1u << lane) - 1u));
-                rays_out[2ull * q] = make_float4(nStart.x, nStart.y, nStart.z, __uint_as_float(slot));
-                rays_out[2ull * q + 1] = make_float4(nDir.x, nDir.y, nDir.z, __uint_as_float(mt_out));
+                st_stream(&rays_out[2ull * q], make_float4(nStart.x, nStart.y, nStart.z, __uint_as_float(slot)));
+                st_stream(&rays_out[2ull * q + 1], make_float4(nDir.x, nDir.y, nDir.z, __uint_as_float(mt_out)));
             }
         }
     }
@@ -645,7 +645,8 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     if (!(prm->flags & VMN_RENDER_ACCUMULATE)) VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
     if (n_local_total == 0 || s_begin == s_end) return VMN_OK;
 
-    const uint64_t cap = c->max_paths;
+    // queue slots and counts are 32-bit: never more than 2^32 - 16 paths in flight, whatever max_paths says
+    const uint64_t cap = c->max_paths < 0xFFFFFFF0ull ? c->max_paths : 0xFFFFFFF0ull;
     const uint64_t chunk = n_local_total < cap ? n_local_total : cap;
     uint32_t batch = 1;
     if (mode == VMN_MODE_FIXED) {
@@ -720,6 +721,8 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 ++c->stats.kernel_launches;
                 int cur = 0;
                 for (uint32_t it = 0; it < max_seg; ++it) {
+                    // a claim counter serves one launch: recycle the block every kMaxClaims bounces (max_segments may exceed it)
+                    if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
                     if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
                     cur ^= 1;
                 }

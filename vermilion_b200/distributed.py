@@ -41,12 +41,25 @@ def render_params(split, rank, world, spp_total, tile=64):
     raise ValueError(f"unknown split {split!r}")
 
 
-def reduce_film(film, group=None):
-    """In-place all-reduce(SUM) of a film-sum tensor (any device; NCCL for CUDA tensors, gloo for CPU tensors)."""
+def reduce_film(film, group=None, force=False):
+    """In-place all-reduce(SUM) of a film-sum tensor (any device; NCCL for CUDA tensors, gloo for CPU tensors).
+
+    Stream order (CUDA): the collective is enqueued on torch's CURRENT stream, not on the engine's. Engine.render() returns with the
+    engine's stream drained, so the film is complete when the collective starts; what follows the collective on the engine's stream
+    (resolve, the next render's memset) must wait for it — use sync_after_reduce() or render_distributed(), which does. `force` runs
+    the collective even in a world of one (tests)."""
     import torch.distributed as dist
-    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+    if dist.is_available() and dist.is_initialized() and (force or dist.get_world_size(group) > 1):
         dist.all_reduce(film, op=dist.ReduceOp.SUM, group=group)
     return film
+
+
+def sync_after_reduce(film):
+    """Orders whatever the engine does next (on ITS stream) after a collective enqueued on torch's current stream: the host waits for
+    that stream. An Engine created without stream= owns a non-blocking stream that nothing else orders against torch's."""
+    if getattr(film, "is_cuda", False):
+        import torch
+        torch.cuda.current_stream(film.device).synchronize()
 
 
 def resolve(film_sum):
@@ -83,7 +96,8 @@ def resolve_bruteforce(film_sum, film_aux):
 
 
 def device_film_tensor(eng, device):
-    """torch view (no copy) of the context's device film buffer, for NCCL."""
+    """torch view (no copy) of the context's device film buffer, for NCCL. The view is only valid until the next Engine.set_camera
+    with a different resolution (vmn_camera_set reallocates the film): take a new view after changing the camera."""
     import torch
     ptr, n = eng.film_device()
 
@@ -108,21 +122,25 @@ def device_film_aux_tensor(eng, device):
     return torch.as_tensor(h, device=device)
 
 
-def render_bruteforce_distributed(eng, device, seed, rank, world, tile=64, shadow=False, group=None):
+def render_bruteforce_distributed(eng, device, seed, rank, world, tile=64, shadow=False, group=None, force_reduce=False):
     """BruteForceTracer across ranks: interleaved tiles (its early-out is sequential per pixel, so pixels — not samples — are split);
     both film planes are zero outside a rank's tiles, so two all-reduce(SUM) assemble the frame exactly. Returns RGBAZ (every rank)."""
     from . import engine as _engine
     eng.render(mode=_engine.MODE_BRUTEFORCE, seed=seed, shadow=shadow, **render_params("tile", rank, world, 0, tile))
     film = device_film_tensor(eng, device)
     aux = device_film_aux_tensor(eng, device)
-    reduce_film(film, group)
-    reduce_film(aux, group)
+    reduce_film(film, group, force_reduce)
+    reduce_film(aux, group, force_reduce)
+    sync_after_reduce(aux)  # the resolve below runs on the engine's stream, the collectives ran on torch's
     return eng.resolve_device(film.data_ptr())  # the context resolves with its own (now reduced) second plane
 
 
-def render_distributed(eng, device, mode, seed, split, rank, world, spp_total, max_segments=5, tile=64, group=None):
-    """Render this rank's share on `eng`, all-reduce the film over the process group, return the RGBAZ image (every rank)."""
+def render_distributed(eng, device, mode, seed, split, rank, world, spp_total, max_segments=5, tile=64, group=None, force_reduce=False):
+    """Render this rank's share on `eng`, all-reduce the film over the process group, return the RGBAZ image (every rank). Safe for an
+    Engine on any stream: the render drains the engine's stream before the collective, and the host waits for the collective's stream
+    before the resolve (and the next render's film memset) is enqueued on the engine's."""
     eng.render(mode=mode, seed=seed, max_segments=max_segments, **render_params(split, rank, world, spp_total, tile))
     film = device_film_tensor(eng, device)
-    reduce_film(film, group)
+    reduce_film(film, group, force_reduce)
+    sync_after_reduce(film)
     return eng.resolve_device(film.data_ptr())

@@ -35,6 +35,18 @@ EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vm
            "vmn_probe_read_bandwidth"]
 
 
+def kernel_source_hash():
+    """sha256 (first 16 hex digits) over the CUDA sources of the library, in name order: stamps measurements that are only valid for
+    the kernels they were captured on (profiles/traffic.json -> bench.py roofline.traffic)."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(_HERE, "csrc", "*.cu")) + glob.glob(os.path.join(_HERE, "csrc", "*.cuh"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("flags", C.c_uint32), ("max_paths", C.c_uint64), ("stream", C.c_void_p)]
 
@@ -55,7 +67,8 @@ class Stats(C.Structure):
     _fields_ = [("n_triangles", C.c_uint64), ("n_nodes", C.c_uint64), ("n_wide_nodes", C.c_uint64), ("node_bytes", C.c_uint64),
                 ("tri_bytes", C.c_uint64), ("build_ms", C.c_double), ("rays_traced", C.c_uint64), ("paths_traced", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("extend_ms", C.c_double), ("shade_ms", C.c_double),
-                ("raygen_ms", C.c_double), ("resolve_ms", C.c_double), ("total_ms", C.c_double), ("kernel_launches", C.c_uint64)]
+                ("raygen_ms", C.c_double), ("resolve_ms", C.c_double), ("total_ms", C.c_double), ("kernel_launches", C.c_uint64),
+                ("wide_depth", C.c_uint64), ("l2_persist_bytes", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
