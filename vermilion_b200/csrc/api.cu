@@ -80,12 +80,14 @@ void camera_matrix(const vmn_camera& cam, float m[16]) {
 
 using namespace vmn;
 
-// Keep the arrays every ray walks (leaf triangles + wide nodes, one allocation) in the L2 while the ray queues — gigabytes per frame,
-// each byte touched once — stream past them: a persisting access-policy window on the context's stream when the arrays fit the device's
-// persisting carve-out (C2: 75 MB of a 126 MB L2); scenes that do not fit (C3, C4) get no window. The queue traffic itself is issued with
-// evict-first loads / stores (VMN_STREAM_HINTS, traverse.cuh). Env VMN_L2_PERSIST=0 switches the window off (A/B).
+// Optional (env VMN_L2_PERSIST=1; OFF by default): a persisting L2 access-policy window over the arrays every ray walks (leaf triangles +
+// wide nodes, one allocation) when they fit the device's persisting carve-out, so that the ray queues — gigabytes per frame, each byte
+// touched once — cannot evict them. Measured on C2 (profiles/r02a_ab_c2.txt, 16 spp frame): k_extend 17.48 -> 17.38 ms, but k_raygen
+// 0.76 -> 0.95 ms and k_shade 7.69 -> 7.98 ms, because the carve-out is taken from the L2 the other stages' read-modify-write traffic
+// lives in: the frame gets 1.5 % SLOWER (26.22 -> 26.61 ms). The evict-first loads / stores on the queue traffic (VMN_STREAM_HINTS,
+// traverse.cuh) are kept: k_extend 17.66 -> 17.48 ms at no cost elsewhere.
 static void apply_l2_policy(vmn_ctx* c) {
-    static const int enabled = [] { const char* e = getenv("VMN_L2_PERSIST"); return e ? atoi(e) : 1; }();
+    static const int enabled = [] { const char* e = getenv("VMN_L2_PERSIST"); return e ? atoi(e) : 0; }();
     int max_persist = 0, max_window = 0;
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
     cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);

@@ -93,7 +93,21 @@ struct Bvh2 {
 #define VMN_STACK_CAP 128 // (the `tinystack` test variant of csrc/Makefile builds with 3 to reach the overflow paths)
 #endif
 constexpr uint32_t kTravStackCap = VMN_STACK_CAP;
-#define VMN_DEVERR_STACK 1u // device error word: a traversal push was dropped (result of that ray is unreliable)
+#define VMN_DEVERR_STACK 1u  // device error word: a traversal push was dropped (result of that ray is unreliable)
+#define VMN_DEVERR_BOUNDS 2u // an index left its array (only raised by the VMN_CHECKED build, see below)
+
+// compute-sanitizer is closed on this GPU pool, so the library carries its own memcheck: the `checked` variant of csrc/Makefile
+// (-DVMN_CHECKED=1) tests every data-dependent index (node, triangle, ray, queue slot, stack entry) against the size of its array before
+// the access and raises VMN_DEVERR_BOUNDS in the device error word, which the next synchronising entry point turns into VMN_ERR_STATE.
+// tools/sanitize_small.py runs every kernel of the library under that build (tests/test_gpu_robustness.py).
+#ifndef VMN_CHECKED
+#define VMN_CHECKED 0
+#endif
+#if VMN_CHECKED
+#define VMN_CHECK(errp, cond) do { if (!(cond)) atomicOr((errp), VMN_DEVERR_BOUNDS); } while (0)
+#else
+#define VMN_CHECK(errp, cond) ((void)0)
+#endif
 
 struct SceneDev {
     uint32_t* err;           // device error word owned by the context (VMN_DEVERR_*), checked at every synchronising entry point
@@ -104,6 +118,7 @@ struct SceneDev {
     const TriRec* tris_orig; // by original id (for barycentrics / getNormal)
     Bvh2 bvh2;
     uint32_t n_tris;
+    uint32_t n_wide;         // wide nodes in use
     uint32_t n_spheres;
     const float* tex;        // texture slot 0 or nullptr
     uint32_t tex_w, tex_h, tex_c;

@@ -85,7 +85,7 @@ vmn_status check_device_error(vmn_ctx* c); // synchronises the stream; VMN_ERR_S
 vmn_status build_bvh(vmn_ctx* c);
 
 // traverse.cu
-uint32_t refill_min(); // idle lanes that trigger a refill in the persistent kernels (env VMN_REFILL, default 8)
+uint32_t refill_min(const vmn_ctx* c); // idle lanes that trigger a refill in the persistent kernels (by scene size; env VMN_REFILL overrides)
 vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags);
 vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_t* d_out);
 vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_raycast_rec* d_out);

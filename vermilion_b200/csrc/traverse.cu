@@ -102,9 +102,13 @@ static int resident_grid(vmn_ctx* c, K kernel) {
     return c->sm_count * per_sm;
 }
 
-uint32_t refill_min() {
-    static const uint32_t v = [] { const char* e = getenv("VMN_REFILL"); int x = e ? atoi(e) : 8; return (uint32_t)(x < 1 ? 1 : (x > 32 ? 32 : x)); }();
-    return v;
+// Idle lanes of a persistent warp that trigger a refill from the ray queue. Measured (profiles/r02a_ab_c2.txt, r02a_ab_c3.txt): 8 on a
+// scene the L2 holds (C2: 4 and 8 equal, 12 is 3.7 % slower); 4 when every node fetch goes to HBM (C3 soup: +1.9 % over 8, 16 is 6 % slower)
+// — a lane that waits for seven neighbours to finish wastes more when each of their steps is a DRAM round trip. VMN_REFILL overrides.
+uint32_t refill_min(const vmn_ctx* c) {
+    static const int env = [] { const char* e = getenv("VMN_REFILL"); int x = e ? atoi(e) : 0; return x < 0 ? 0 : (x > 32 ? 32 : x); }();
+    if (env) return (uint32_t)env;
+    return c->trav_bytes > (96ull << 20) ? 4u : 8u;
 }
 
 static vmn_status reset_counters(vmn_ctx* c) {
@@ -125,7 +129,7 @@ vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_h
     if (n) {
         VMN_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
 #define LAUNCH(W, C)                                                                                                           \
-    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt, refill_min())
+    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt, refill_min(c))
         if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
         else { if (count) LAUNCH(false, true); else LAUNCH(false, false); }
 #undef LAUNCH
@@ -141,7 +145,7 @@ vmn_status launch_occluded(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, uint8_
     vmn_status s = reset_counters(c);
     if (s != VMN_OK) return s;
     if (n) {
-        k_occluded<<<resident_grid(c, k_occluded), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, c->counters.as<unsigned long long>(), refill_min());
+        k_occluded<<<resident_grid(c, k_occluded), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, c->counters.as<unsigned long long>(), refill_min(c));
         VMN_CUDA(c, cudaGetLastError());
     }
     c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;
@@ -153,7 +157,7 @@ vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_ray
     if (s != VMN_OK) return s;
     if (n) {
         k_raycast<<<resident_grid(c, k_raycast), kTraceBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), d_rays, n, d_out,
-                                                                            c->counters.as<unsigned long long>(), refill_min());
+                                                                            c->counters.as<unsigned long long>(), refill_min(c));
         VMN_CUDA(c, cudaGetLastError());
     }
     c->stats.rays_traced = n; c->stats.kernel_launches = n ? 1 : 0;

@@ -206,6 +206,7 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
             else atomicOr(sc.err, VMN_DEVERR_STACK);
         }
+        VMN_CHECK(sc.err, nidx < sc.n_wide && s.sp >= 0 && s.sp <= (int)kTravStackCap);
         const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
 #if VMN_SIGNED_LOADS
         // The near plane of an axis is the low plane for a positive direction and the high plane for a negative one. Instead of loading
@@ -320,6 +321,7 @@ __device__ __forceinline__ void trav_tris(Trav& s, const SceneDev& sc, TravCount
         const uint32_t i = __ffs(s.tg.y) - 1u;
         s.tg.y &= s.tg.y - 1u;
         const uint32_t ti = s.tg.x + i;
+        VMN_CHECK(sc.err, ti < sc.n_tris);
         const TriRec T = load_tri(sc.tris + ti);
         if (COUNT) ++cnt->tris;
         float ct;
@@ -394,6 +396,7 @@ __device__ __forceinline__ void trav_tris_coop(Trav& s, bool active, const Scene
             uint32_t b = rank == 0u ? o_bits : (rank == 1u ? b1 : b2);
             for (uint32_t k = rank; k > 2u; --k) b &= b - 1u;
             const uint32_t ti = o_base + (__ffs(b) - 1u);
+            VMN_CHECK(sc.err, ti < sc.n_tris && b != 0u && owner < 32u);
             const TriRec T = load_tri(sc.tris + ti);
             if (COUNT) ++cnt->tris;
             float ct;
@@ -491,6 +494,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
                 if (r < take) {
                     V3 o, d;
                     ray = wbase + r;
+                    VMN_CHECK(sc.err, ray < n);
                     load(ray, &o, &d);
                     if (trav_init(s, sc, o, d)) active = true; else store(ray, s);
                 }
@@ -540,6 +544,7 @@ __device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, f
     while (true) {
         if (node >= nint) {
             const uint32_t k = (uint32_t)(node - nint);
+            VMN_CHECK(sc.err, k < n);
             const TriRec T = load_tri(sc.tris_sorted + k);
             if (COUNT) ++cnt->tris;
             float ct;
@@ -549,6 +554,7 @@ __device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, f
             continue;
         }
         if (COUNT) ++cnt->nodes;
+        VMN_CHECK(sc.err, node >= 0 && node < nint);
         const int2 c = __ldg(&sc.bvh2.child[node]);
         float tn[2]; bool hit[2];
 #pragma unroll
@@ -634,6 +640,7 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
     }
     if (r.material) {
         V3 hp = o + d * bvh_t; // bvh.cpp:140
+        VMN_CHECK(sc.err, tri_id < sc.n_tris);
         const TriRec T = load_tri(sc.tris_orig + tri_id);
         float w1, w2;
         tri_bary(T, hp, &w1, &w2);

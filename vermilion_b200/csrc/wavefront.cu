@@ -237,6 +237,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             const float4 ra = ld_stream(&rays[2 * i]), rb = ld_stream(&rays[2 * i + 1]);
             const float2 hr = ld_stream(&hits[i]);
             slot = __float_as_uint(ra.w);
+            VMN_CHECK(sc.err, (uint64_t)slot < rp.n_local * (rp.batch ? rp.batch : 1u));
             V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
             const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y));
             // Path state traffic: the throughput stays exactly (1,1,1,1) until a textured diffuse bounce scales it, and the radiance only
@@ -328,6 +329,7 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             qb = __shfl_sync(0xffffffffu, qb, leader);
             if (alive) {
                 const uint32_t q = qb + __popc(ballot & ((1u << lane) - 1u));
+                VMN_CHECK(sc.err, q < n); // survivors never outnumber the rays that came in
                 st_stream(&rays_out[2ull * q], make_float4(nStart.x, nStart.y, nStart.z, __uint_as_float(slot)));
                 st_stream(&rays_out[2ull * q + 1], make_float4(nDir.x, nDir.y, nDir.z, __uint_as_float(mt_out)));
             }
@@ -518,9 +520,9 @@ static vmn_status launch_extend(vmn_ctx* c, PathPool* p, int cur, uint32_t it, S
     const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
     if (clk) clk->begin(ST_EXTEND);
     if (count)
-        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
+        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c));
     else
-        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min());
+        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c));
     if (clk) clk->end();
     ++c->stats.kernel_launches;
     return VMN_OK;
