@@ -39,6 +39,7 @@ typedef enum {
     VMN_ERR_INVALID = 1, /* bad argument */
     VMN_ERR_CUDA = 2,    /* CUDA runtime / launch failure, or no device */
     VMN_ERR_OOM = 3,     /* device or host allocation failed */
+    VMN_ERR_NCCL = 5,    /* a collective failed, or libnccl.so.2 could not be loaded (vmn_dist_* only) */
     VMN_ERR_STATE = 4    /* call order violated (e.g. render before commit), or a device-side consistency check failed
                           * (a traversal stack overflowed: the results of that call are unreliable) */
 } vmn_status;
@@ -208,6 +209,57 @@ vmn_status vmn_get_stats(vmn_ctx* ctx, vmn_stats* out);
  * bandwidth in GB/s. A working set well below the L2 size (126 MB) measures L2 read bandwidth — what bounds k_extend on a scene
  * that stays L2-resident (C2) —, one well above it HBM read bandwidth. Not on the render path. */
 vmn_status vmn_probe_read_bandwidth(vmn_ctx* ctx, uint64_t bytes, uint32_t passes, double* gb_per_s);
+
+/* ---- several GPUs behind one call --------------------------------------------------------------------------------------------
+ * The reference's host makes ONE mIntegrator->Render(mCameras, mMeshEngine) per frame (core/engines/renderEngine.cpp:147-166) and
+ * parallelises inside it over pixels (core/integrators/pathtracer.cpp:226-227). A vmn_dist group keeps that shape for 1..16 B200s
+ * of one node: it owns one context per device, splits the frame, and assembles the film on the root (rank 0) over NCCL / NVLink:
+ *   sample slices (FIXED mode): ncclReduce(sum) of the (sum r, g, b, n) film to the root;
+ *   interleaved tiles (any mode): every rank sends the pixels of ITS tiles (1/N of the film), the root receives and unpacks them.
+ * The scene goes up once on the root's PCIe link and is ncclBroadcast to the other devices (VMN_DIST_SCENE_BROADCAST), each device
+ * builds its own BVH; only the root resolves and reads the image back. NCCL is loaded at run time (dlopen): a single-GPU user of this
+ * library never needs it.
+ *   local group: one process, N devices, one host thread per device (ncclCommInitAll) — what B200PathTracer and vermilion_headless
+ *                --gpus N use;
+ *   rank group:  one process per device (torchrun): rank 0 calls vmn_dist_unique_id and hands the 128 bytes to the others by any
+ *                means (bench.py: torch.distributed broadcast), every rank calls vmn_dist_create_rank. All vmn_dist_* calls are
+ *                then collective: every rank makes them in the same order. */
+typedef struct vmn_dist vmn_dist;
+#define VMN_DIST_MAX_RANKS 16
+#define VMN_DIST_ID_BYTES 128
+enum { VMN_DIST_SPLIT_SAMPLES = 0, VMN_DIST_SPLIT_TILES = 1 };
+#define VMN_DIST_SCENE_BROADCAST 1u /* vmn_dist_scene_set_triangles: read the host arrays on the root only and broadcast them over NVLink
+                                     * (the other ranks of a rank group may pass NULL / 0); without it every member uploads the arrays */
+#define VMN_DIST_RENDER_ASSEMBLE 0x100u /* vmn_render_params.flags, sample slices with VMN_RENDER_ACCUMULATE: progressive passes stay in
+                                         * each rank's own film; the pass that carries this flag also reduces the films to the root */
+typedef struct {
+    uint32_t world, local;                     /* ranks in the group / members in this process */
+    double render_ms[VMN_DIST_MAX_RANKS];      /* device time of the last vmn_render of each LOCAL member */
+    double frame_ms, collective_ms, scene_ms;  /* root's stream: render + assembly, assembly alone; last broadcast scene upload */
+    uint64_t rays_traced;                      /* sum over the local members */
+} vmn_dist_stats;
+
+vmn_status vmn_dist_create_local(const int32_t* devices, uint32_t n, uint32_t cfg_flags, uint64_t max_paths, vmn_dist** out);
+vmn_status vmn_dist_unique_id(uint8_t* id /* VMN_DIST_ID_BYTES */);
+vmn_status vmn_dist_create_rank(const uint8_t* id, uint32_t rank, uint32_t world, const vmn_config* cfg, vmn_dist** out);
+void vmn_dist_destroy(vmn_dist* g);
+const char* vmn_dist_last_error(const vmn_dist* g);
+uint32_t vmn_dist_world(const vmn_dist* g);
+uint32_t vmn_dist_rank(const vmn_dist* g);           /* rank of this process's first member (0 in a local group) */
+uint32_t vmn_dist_local_count(const vmn_dist* g);
+vmn_ctx* vmn_dist_context(vmn_dist* g, uint32_t local_index); /* borrowed: a member's context (stats, ray queries) */
+/* scene / camera: as the vmn_scene_* / vmn_camera_set calls, applied to every member */
+vmn_status vmn_dist_scene_set_triangles(vmn_dist* g, const float* pos, const float* nrm, const float* uv, uint64_t n, uint32_t flags);
+vmn_status vmn_dist_scene_set_spheres(vmn_dist* g, const vmn_sphere* spheres, uint32_t n);
+vmn_status vmn_dist_scene_set_texture(vmn_dist* g, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t c);
+vmn_status vmn_dist_scene_commit(vmn_dist* g);
+vmn_status vmn_dist_camera_set(vmn_dist* g, const vmn_camera* cam);
+/* replaces the one Render call of renderEngine.cpp:164 for the whole group: params as vmn_render (tile / pixel range fields zero: the
+ * group chooses the shares; sample_begin / sample_end select the pass of a progressive render), split = VMN_DIST_SPLIT_*,
+ * tile_size 0 = 64. On return the root's film holds the assembled frame. */
+vmn_status vmn_dist_render(vmn_dist* g, const vmn_render_params* params, int32_t split, uint32_t tile_size);
+vmn_status vmn_dist_read_image(vmn_dist* g, float* dst, int32_t layout); /* root: as vmn_read_image; other ranks: no-op */
+vmn_status vmn_dist_get_stats(vmn_dist* g, vmn_dist_stats* out);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

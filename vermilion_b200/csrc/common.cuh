@@ -128,6 +128,29 @@ struct SceneDev {
 
 struct __align__(16) SphereDev { float cx, cy, cz, r; float ex, ey, ez; uint32_t flags; float nx, ny, nz, pad; };
 
+// which pixels this context renders: a contiguous range or interleaved square tiles
+struct PixelMap {
+    uint32_t width, height;
+    uint64_t begin;       // contiguous: first pixel
+    uint32_t tile, rank, world, tiles_x;
+};
+
+__device__ __forceinline__ bool map_pixel(const PixelMap& m, uint64_t lp, uint64_t* pixel) {
+    if (m.tile == 0) { *pixel = m.begin + lp; return *pixel < (uint64_t)m.width * m.height; }
+    const uint32_t tt = m.tile * m.tile;
+    uint64_t j; uint32_t w;
+    if ((lp >> 32) == 0) { const uint32_t j32 = (uint32_t)lp / tt; j = j32; w = (uint32_t)lp - j32 * tt; } // the usual case: 32-bit divides
+    else { j = lp / tt; w = (uint32_t)(lp % tt); }
+    const uint64_t t = j * m.world + m.rank;
+    uint32_t ty, tx;
+    if ((t >> 32) == 0) { ty = (uint32_t)t / m.tiles_x; tx = (uint32_t)t - ty * m.tiles_x; }
+    else { ty = (uint32_t)(t / m.tiles_x); tx = (uint32_t)(t % m.tiles_x); }
+    const uint32_t x = tx * m.tile + (w % m.tile), y = ty * m.tile + (w / m.tile);
+    if (x >= m.width || y >= m.height) return false;
+    *pixel = (uint64_t)y * m.width + x;
+    return true;
+}
+
 // ---- Philox4x32-10, key (seed_lo, seed_hi), counter (pixel_lo, pixel_hi, sample, block) ------------
 __host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;

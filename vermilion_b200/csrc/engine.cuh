@@ -100,6 +100,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* p);
 // d_aux: BRUTEFORCE second plane or nullptr (PathTracer film: alpha 1, depth = samples)
 vmn_status film_resolve(vmn_ctx* c, const float* d_sum, const float* d_aux, float* d_rgbaz, uint64_t npix);
 vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, const float* d_aux, uint8_t* d_rgba, float* d_depth, uint64_t npix);
+vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* out, uint64_t* n_local_total); // this context's share of the frame
 void pool_destroy(vmn_ctx* c);
 void camera_matrix(const vmn_camera& cam, float m[16]);
 

@@ -19,29 +19,6 @@ namespace vmn {
 
 constexpr int kWfBlock = 128;
 
-// which pixels this context renders: a contiguous range or interleaved square tiles
-struct PixelMap {
-    uint32_t width, height;
-    uint64_t begin;       // contiguous: first pixel
-    uint32_t tile, rank, world, tiles_x;
-};
-
-__device__ __forceinline__ bool map_pixel(const PixelMap& m, uint64_t lp, uint64_t* pixel) {
-    if (m.tile == 0) { *pixel = m.begin + lp; return *pixel < (uint64_t)m.width * m.height; }
-    const uint32_t tt = m.tile * m.tile;
-    uint64_t j; uint32_t w;
-    if ((lp >> 32) == 0) { const uint32_t j32 = (uint32_t)lp / tt; j = j32; w = (uint32_t)lp - j32 * tt; } // the usual case: 32-bit divides
-    else { j = lp / tt; w = (uint32_t)(lp % tt); }
-    const uint64_t t = j * m.world + m.rank;
-    uint32_t ty, tx;
-    if ((t >> 32) == 0) { ty = (uint32_t)t / m.tiles_x; tx = (uint32_t)t - ty * m.tiles_x; }
-    else { ty = (uint32_t)(t / m.tiles_x); tx = (uint32_t)(t % m.tiles_x); }
-    const uint32_t x = tx * m.tile + (w % m.tile), y = ty * m.tile + (w / m.tile);
-    if (x >= m.width || y >= m.height) return false;
-    *pixel = (uint64_t)y * m.width + x;
-    return true;
-}
-
 struct CamDev {
     float m[16];
     float px, py, pz;
@@ -607,7 +584,7 @@ vmn_status film_pack_rgba8(vmn_ctx* c, const float* d_sum, const float* d_aux, u
 }
 
 // this context's share of the frame: interleaved tiles or a contiguous pixel range
-static vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* out, uint64_t* n_local_total) {
+vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* out, uint64_t* n_local_total) {
     const uint64_t npix = c->film_pixels;
     PixelMap pm{};
     pm.width = c->cam.width; pm.height = c->cam.height;

@@ -25,14 +25,22 @@ CFG_COUNTERS = 1
 RENDER_ACCUMULATE = 1
 RENDER_BF_SHADOW = 2
 ISECT_BVH2 = 1
-STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE"}
+STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE", 5: "NCCL"}
+DIST_SPLIT_SAMPLES, DIST_SPLIT_TILES = 0, 1
+DIST_SCENE_BROADCAST = 1
+DIST_RENDER_ASSEMBLE = 0x100
+DIST_MAX_RANKS, DIST_ID_BYTES = 16, 128
 
 EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vmn_set_stream", "vmn_synchronize",
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
            "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
            "vmn_film_resolve_device", "vmn_film_upload", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats",
-           "vmn_probe_read_bandwidth"]
+           "vmn_probe_read_bandwidth",
+           "vmn_dist_create_local", "vmn_dist_unique_id", "vmn_dist_create_rank", "vmn_dist_destroy", "vmn_dist_last_error", "vmn_dist_world",
+           "vmn_dist_rank", "vmn_dist_local_count", "vmn_dist_context", "vmn_dist_scene_set_triangles", "vmn_dist_scene_set_spheres",
+           "vmn_dist_scene_set_texture", "vmn_dist_scene_commit", "vmn_dist_camera_set", "vmn_dist_render", "vmn_dist_read_image",
+           "vmn_dist_get_stats"]
 
 
 def kernel_source_hash():
@@ -72,6 +80,11 @@ class Stats(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class DistStats(C.Structure):
+    _fields_ = [("world", C.c_uint32), ("local", C.c_uint32), ("render_ms", C.c_double * 16), ("frame_ms", C.c_double),
+                ("collective_ms", C.c_double), ("scene_ms", C.c_double), ("rays_traced", C.c_uint64)]
 
 
 def camera_from_settings(width, height, position, rotation_deg, back_distance=6.0, back_size=(3.6, 2.4), spp=16):
@@ -136,6 +149,26 @@ def load_library():
     L.vmn_read_image_rgba8.argtypes = [vp, vp, vp]
     L.vmn_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.vmn_probe_read_bandwidth.argtypes = [vp, u64, u32, C.POINTER(C.c_double)]
+    L.vmn_dist_create_local.argtypes = [vp, u32, u32, u64, C.POINTER(vp)]
+    L.vmn_dist_unique_id.argtypes = [vp]
+    L.vmn_dist_create_rank.argtypes = [vp, u32, u32, C.POINTER(Config), C.POINTER(vp)]
+    L.vmn_dist_destroy.argtypes = [vp]
+    L.vmn_dist_destroy.restype = None
+    L.vmn_dist_last_error.argtypes = [vp]
+    L.vmn_dist_last_error.restype = C.c_char_p
+    for f in (L.vmn_dist_world, L.vmn_dist_rank, L.vmn_dist_local_count):
+        f.argtypes = [vp]
+        f.restype = u32
+    L.vmn_dist_context.argtypes = [vp, u32]
+    L.vmn_dist_context.restype = vp
+    L.vmn_dist_scene_set_triangles.argtypes = [vp, vp, vp, vp, u64, u32]
+    L.vmn_dist_scene_set_spheres.argtypes = [vp, vp, u32]
+    L.vmn_dist_scene_set_texture.argtypes = [vp, u32, vp, u32, u32, u32]
+    L.vmn_dist_scene_commit.argtypes = [vp]
+    L.vmn_dist_camera_set.argtypes = [vp, C.POINTER(Camera)]
+    L.vmn_dist_render.argtypes = [vp, C.POINTER(RenderParams), i32, u32]
+    L.vmn_dist_read_image.argtypes = [vp, vp, i32]
+    L.vmn_dist_get_stats.argtypes = [vp, C.POINTER(DistStats)]
     _LIB = L
     return L
 
@@ -314,3 +347,124 @@ class Engine:
         s = Stats()
         self._chk(self.L.vmn_get_stats(self.h, C.byref(s)), "vmn_get_stats")
         return s.as_dict()
+
+
+class DistGroup:
+    """One vmn_dist group (include/vermilion_b200.h): several B200s behind one render call. local(devices): one process, one member per
+    device; rank(id, rank, world, ...): one process per device (torchrun), `id` = unique_id() of rank 0 handed to every rank."""
+
+    def __init__(self, handle, lib):
+        self.h, self.L, self.cam = handle, lib, None
+
+    @staticmethod
+    def unique_id():
+        L = load_library()
+        buf = (C.c_uint8 * DIST_ID_BYTES)()
+        st = L.vmn_dist_unique_id(buf)
+        if st != 0:
+            raise VmnError(f"vmn_dist_unique_id: {STATUS.get(st, st)} (libnccl.so.2 not loadable?)")
+        return bytes(buf)
+
+    @classmethod
+    def _made(cls, L, st, h, what):
+        if st != 0:
+            msg = L.vmn_dist_last_error(h).decode() if h else "allocation failed"
+            if h:
+                L.vmn_dist_destroy(h)
+            raise VmnError(f"{what}: {STATUS.get(st, st)}: {msg}")
+        return cls(h, L)
+
+    @classmethod
+    def local(cls, devices, counters=False, max_paths=0):
+        L = load_library()
+        h = C.c_void_p()
+        arr = (C.c_int32 * len(devices))(*devices)
+        st = L.vmn_dist_create_local(arr, len(devices), CFG_COUNTERS if counters else 0, max_paths, C.byref(h))
+        return cls._made(L, st, h, "vmn_dist_create_local")
+
+    @classmethod
+    def rank(cls, uid, rank, world, device=0, counters=False, max_paths=0, stream=None):
+        L = load_library()
+        h = C.c_void_p()
+        cfg = Config(device, CFG_COUNTERS if counters else 0, max_paths, stream)
+        buf = (C.c_uint8 * DIST_ID_BYTES)(*uid) if uid is not None else None
+        st = L.vmn_dist_create_rank(buf, rank, world, C.byref(cfg), C.byref(h))
+        return cls._made(L, st, h, "vmn_dist_create_rank")
+
+    def _chk(self, st, what):
+        if st != 0:
+            raise VmnError(f"{what}: {STATUS.get(st, st)}: {self.L.vmn_dist_last_error(self.h).decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.vmn_dist_destroy(self.h)
+            self.h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def world(self):
+        return self.L.vmn_dist_world(self.h)
+
+    @property
+    def my_rank(self):
+        return self.L.vmn_dist_rank(self.h)
+
+    def set_scene(self, pos, nrm=None, uv=None, spheres=None, texture=None, texture1=None, broadcast=False):
+        """pos / nrm / uv may be None on the non-root ranks of a rank group when broadcast=True (the root's arrays cross NVLink)."""
+        pos = None if pos is None else np.ascontiguousarray(pos, np.float32).reshape(-1, 9)
+        nrm = None if nrm is None else np.ascontiguousarray(nrm, np.float32).reshape(-1, 9)
+        uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 6)
+        n = 0 if pos is None else len(pos)
+        self._chk(self.L.vmn_dist_scene_set_triangles(self.h, _p(pos), _p(nrm), _p(uv), n, DIST_SCENE_BROADCAST if broadcast else 0),
+                  "vmn_dist_scene_set_triangles")
+        sp = reference_spheres() if spheres is None else np.ascontiguousarray(spheres, SPHERE)
+        self._chk(self.L.vmn_dist_scene_set_spheres(self.h, _p(sp) if len(sp) else None, len(sp)), "vmn_dist_scene_set_spheres")
+        for slot, tex in ((0, texture), (1, texture1)):
+            if tex is not None:
+                t = np.ascontiguousarray(tex, np.float32)
+                self._chk(self.L.vmn_dist_scene_set_texture(self.h, slot, _p(t), t.shape[1], t.shape[0], t.shape[2]), "vmn_dist_scene_set_texture")
+        self._chk(self.L.vmn_dist_scene_commit(self.h), "vmn_dist_scene_commit")
+
+    def set_camera(self, cam):
+        self.cam = cam
+        self._chk(self.L.vmn_dist_camera_set(self.h, C.byref(cam)), "vmn_dist_camera_set")
+
+    def render(self, mode=MODE_FIXED, seed=1, max_segments=5, split=DIST_SPLIT_SAMPLES, tile=64, sample_begin=0, sample_end=0,
+               accumulate=False, assemble=False, shadow=False):
+        flags = (RENDER_ACCUMULATE if accumulate else 0) | (RENDER_BF_SHADOW if shadow else 0) | (DIST_RENDER_ASSEMBLE if assemble else 0)
+        prm = RenderParams(mode, max_segments, seed, 0, 0, sample_begin, sample_end, 0, 0, 0, flags)
+        self._chk(self.L.vmn_dist_render(self.h, C.byref(prm), split, tile), "vmn_dist_render")
+
+    def read_image(self, layout=FILM_RGBAZ, out=None):
+        """the assembled frame on the root; None on the other ranks of a rank group"""
+        if self.my_rank != 0:
+            self._chk(self.L.vmn_dist_read_image(self.h, None, layout), "vmn_dist_read_image")
+            return None
+        npx = self.cam.width * self.cam.height
+        shape = (npx, 5 if layout == FILM_RGBAZ else 4)
+        if out is None:
+            out = np.empty(shape, np.float32)
+        assert out.dtype == np.float32 and out.shape == shape and out.flags.c_contiguous
+        self._chk(self.L.vmn_dist_read_image(self.h, _p(out), layout), "vmn_dist_read_image")
+        return out
+
+    def stats(self):
+        s = DistStats()
+        self._chk(self.L.vmn_dist_get_stats(self.h, C.byref(s)), "vmn_dist_get_stats")
+        d = {k: getattr(s, k) for k, _ in s._fields_ if k != "render_ms"}
+        d["render_ms"] = list(s.render_ms)[:s.local]
+        return d
+
+    def member_stats(self, i=0):
+        st = Stats()
+        ctx = self.L.vmn_dist_context(self.h, i)
+        if not ctx or self.L.vmn_get_stats(ctx, C.byref(st)) != 0:
+            raise VmnError("vmn_get_stats on a group member")
+        return st.as_dict()
