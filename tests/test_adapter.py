@@ -111,10 +111,11 @@ def test_adapter_progressive_checkpoints_resume(tmp_path):
     path = str(tmp_path / "film.vmn").encode()
     try:
         L.adapter_set_checkpoint(path, 4)
-        rc, img, _, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
+        rc, img, full_rays, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
         assert rc == 0, err
         assert np.array_equal(img.view(np.uint32), one_shot.view(np.uint32))
         film, hdr = film_io.checkpoint_load(path.decode())
+        assert hdr.frame_fingerprint != 0
         assert hdr.spp_done == 16 and hdr.spp_total == 16 and hdr.seed == 11
         # rebuild the state of a run interrupted after 8 spp and let the adapter resume it
         from vermilion_b200 import engine
@@ -122,11 +123,26 @@ def test_adapter_progressive_checkpoints_resume(tmp_path):
             eng.set_scene(pos, nrm, uv)
             eng.set_camera(engine.camera_from_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16))
             eng.render(mode=engine.MODE_FIXED, seed=11, sample_begin=0, sample_end=8)
-            film_io.checkpoint_save(path.decode(), eng.read_image(engine.FILM_SUM), 64, 48, 8, 16, 11)
+            half = eng.read_image(engine.FILM_SUM)
+        film_io.checkpoint_save(path.decode(), half, 64, 48, 8, 16, 11, frame_fingerprint=hdr.frame_fingerprint)
         rc, img, nrays, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
         assert rc == 0, err
         assert np.array_equal(img.view(np.uint32), one_shot.view(np.uint32))
         assert film_io.checkpoint_info(path.decode()).spp_done == 16
+        assert nrays < 0.75 * full_rays  # only the second half was traced
+        # a checkpoint of ANOTHER frame with the same size / spp / seed (here: a finished film full of garbage whose fingerprint
+        # does not match this camera and scene) must be ignored, not returned as the image
+        film_io.checkpoint_save(path.decode(), np.full_like(half, 1e6), 64, 48, 16, 16, 11, frame_fingerprint=hdr.frame_fingerprint ^ 1)
+        rc, img, nrays, err = adapter_render(ref, cs, RGBAZ, checker.MODE_FIXED, 11)
+        assert rc == 0, err
+        assert np.array_equal(img.view(np.uint32), one_shot.view(np.uint32)) and nrays == full_rays
+        # ... and so must the checkpoint of the same scene seen from another camera pose
+        cs2 = checker.camera_settings(64, 48, (50, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 16)
+        rc, img2, _, err = adapter_render(ref, cs2, RGBAZ, checker.MODE_FIXED, 11)
+        assert rc == 0, err
+        L.adapter_set_checkpoint(None, 0)
+        rc, want2, _, err = adapter_render(ref, cs2, RGBAZ, checker.MODE_FIXED, 11)
+        assert rc == 0 and np.array_equal(img2.view(np.uint32), want2.view(np.uint32)) and not np.array_equal(img2, one_shot)
     finally:
         L.adapter_set_checkpoint(None, 0)
 
@@ -157,3 +173,73 @@ def test_adapter_renders_every_camera_of_the_list():
     for a, b in zip(outs, singles):
         assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
         assert a[:, :3].max() > 0
+
+
+@pytest.mark.gpu
+@needs_adapter
+def test_adapter_scene_cache_is_keyed_on_content():
+    """ADVICE r1 / VERDICT r1: the adapter used to key its GPU scene on (MeshEngine pointer, face count, texture count). One integrator
+    renders, the MeshEngine's vertices are moved IN PLACE (same pointer, same counts), and it renders again: the second film must be the
+    moved scene's, i.e. equal to what a fresh engine renders from the moved triangles."""
+    from vermilion_b200 import engine
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    ref = checker.Ref(pos, nrm, uv)
+    cs = checker.camera_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 8)
+    L = C.CDLL(ADAPTER)
+    L.adapter_render_edit_render.argtypes = [C.c_void_p, C.POINTER(checker.RefCameraSettings), C.c_int, C.c_uint64, C.c_float, C.c_void_p, C.c_void_p,
+                                             C.c_char_p, C.c_int]
+    a, b = np.zeros((64 * 48, 5), np.float32), np.zeros((64 * 48, 5), np.float32)
+    err = C.create_string_buffer(512)
+    rc = L.adapter_render_edit_render(ref.h, C.byref(cs), checker.MODE_FIXED, 4, 120.0, a.ctypes.data, b.ctypes.data, err, 512)
+    assert rc == 0, err.value
+    moved = pos.copy()
+    moved[:, 1::3] += np.float32(120.0)
+    with engine.Engine(device=0) as eng:
+        cam = engine.camera_from_settings(64, 48, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 2.7), 8)
+        for p, got in ((pos, a), (moved, b)):
+            eng.set_scene(p, nrm, uv)
+            eng.set_camera(cam)
+            eng.render(mode=engine.MODE_FIXED, seed=4)
+            assert np.array_equal(eng.read_image().view(np.uint32), got.view(np.uint32))
+    assert not np.array_equal(a, b)
+
+
+def _adapter_devices(devs, split_samples=False):
+    L = C.CDLL(ADAPTER)
+    L.adapter_set_devices.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_int]
+    L.adapter_set_devices((C.c_int * len(devs))(*devs), len(devs), int(split_samples))
+
+
+def _gpu_lists():
+    import torch
+    lists = [[0, 0, 0]]  # one GPU, three members: peer-copy exchange (NCCL refuses duplicate devices)
+    if torch.cuda.device_count() >= 2:
+        lists.append(list(range(min(torch.cuda.device_count(), 4))))  # NCCL over NVLink
+    return lists
+
+
+@pytest.mark.gpu
+@needs_adapter
+@pytest.mark.parametrize("mode", [checker.MODE_COMPAT, checker.MODE_FIXED, 2])
+def test_adapter_on_several_devices_is_bit_identical_to_one(mode):
+    """B200Options::devices: the ONE Render call of the host (renderEngine.cpp:164) spread over several devices by interleaved tiles;
+    Camera::mImage is bit-identical to the single-device frame for every estimator (PathTracer compat / fixed, BruteForceTracer)."""
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    ref = checker.Ref(pos, nrm, uv)
+    cs = checker.camera_settings(200, 136, (0, 500, 1900), (0, 5, 0), 6.0, (3.6, 3.6 * 136 / 200), 16)
+    rc, one, rays_one, err = adapter_render(ref, cs, RGBAZ, mode, 11)
+    assert rc == 0, err
+    try:
+        for devs in _gpu_lists():
+            _adapter_devices(devs)
+            rc, img, rays, err = adapter_render(ref, cs, RGBAZ, mode, 11)
+            assert rc == 0, err
+            assert np.array_equal(img.view(np.uint32), one.view(np.uint32)), devs
+            assert rays == rays_one
+            if mode == checker.MODE_FIXED:
+                _adapter_devices(devs, split_samples=True)
+                rc, img, rays, err = adapter_render(ref, cs, RGBAZ, mode, 11)
+                assert rc == 0, err
+                assert np.array_equal(img[:, 3:], one[:, 3:]) and np.allclose(img, one, rtol=1e-5, atol=1e-6) and rays == rays_one
+    finally:
+        _adapter_devices([])

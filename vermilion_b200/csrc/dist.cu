@@ -478,11 +478,16 @@ vmn_status vmn_dist_render(vmn_dist* g, const vmn_render_params* p, int32_t spli
     if (W > 1) {
         const uint64_t npix = (uint64_t)cam.width * cam.height;
         if (split == VMN_DIST_SPLIT_SAMPLES) {
-            // accumulate flag: the root's film already holds earlier passes; the other ranks' films hold only their own passes as
-            // well (they accumulate locally too), so reducing after EVERY pass would count earlier passes twice -> reduce only the
-            // ranks' films into the root when the caller asks for the assembled frame (VMN_RENDER_ACCUMULATE passes stay local).
-            if (!(p->flags & VMN_RENDER_ACCUMULATE) || (p->flags & VMN_DIST_RENDER_ASSEMBLE))
+            // Progressive passes (VMN_RENDER_ACCUMULATE) stay in each rank's own film. A pass that asks for the assembled frame
+            // (VMN_DIST_RENDER_ASSEMBLE, or any non-accumulating pass) reduces the films into the root's and then clears the other
+            // ranks' films, so that what they hold is never counted twice by a later assembly: the root's film is the running total.
+            if (!(p->flags & VMN_RENDER_ACCUMULATE) || (p->flags & VMN_DIST_RENDER_ASSEMBLE)) {
                 s = reduce_to_root(g, [](vmn_dist::Member& mb) { return mb.ctx->film.as<float>(); }, 4 * npix);
+                if (s != VMN_OK) return s;
+                if (!g->use_nccl) { auto* r = g->root(); DCUDA(g, cudaSetDevice(r->device)); DCUDA(g, cudaStreamSynchronize(r->ctx->stream)); } // peer copies read the films on the root's stream
+                for (auto& mb : g->m)
+                    if (mb.rank != 0) { DCUDA(g, cudaSetDevice(mb.device)); DCUDA(g, cudaMemsetAsync(mb.ctx->film.p, 0, 16 * npix, mb.ctx->stream)); }
+            }
         } else {
             s = gather_tiles<4>(g, [](vmn_dist::Member& mb) { return mb.ctx->film.as<float>(); }, cam.width, cam.height, tile);
             if (s == VMN_OK && p->mode == VMN_MODE_BRUTEFORCE)

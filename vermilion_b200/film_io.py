@@ -11,7 +11,7 @@ _LIB = None
 
 class CheckpointHeader(C.Structure):
     _fields_ = [("magic", C.c_char * 8), ("width", C.c_uint32), ("height", C.c_uint32), ("spp_done", C.c_uint32), ("spp_total", C.c_uint32),
-                ("seed", C.c_uint64), ("max_segments", C.c_uint32), ("crc32", C.c_uint32)]
+                ("seed", C.c_uint64), ("max_segments", C.c_uint32), ("crc32", C.c_uint32), ("frame_fingerprint", C.c_uint64)]
 
 
 def lib():
@@ -46,10 +46,10 @@ def write_pfm(path, data, width, height, channels):
     _chk(lib().vmnh_write_pfm(os.fsencode(path), data.ctypes.data, width, height, channels), "vmnh_write_pfm")
 
 
-def checkpoint_save(path, film_sum, width, height, spp_done, spp_total, seed, max_segments=5):
+def checkpoint_save(path, film_sum, width, height, spp_done, spp_total, seed, max_segments=5, frame_fingerprint=0):
     film_sum = np.ascontiguousarray(film_sum, np.float32)
     assert film_sum.size == width * height * 4
-    h = CheckpointHeader(b"VMNFILM1", width, height, spp_done, spp_total, seed, max_segments, 0)
+    h = CheckpointHeader(b"VMNFILM2", width, height, spp_done, spp_total, seed, max_segments, 0, frame_fingerprint)
     _chk(lib().vmnh_checkpoint_save(os.fsencode(path), film_sum.ctypes.data, C.byref(h)), "vmnh_checkpoint_save")
 
 

@@ -29,13 +29,19 @@ namespace Vermilion
     struct B200Options
     {
         int device = 0;
+        // several B200s of this node behind the ONE Render call the host makes (renderEngine.cpp:164): empty = {device}. The frame is
+        // split by interleaved 64x64 tiles (any estimator) or, with splitSamples, by sample slices (FIXED mode); the film is assembled
+        // on devices[0] over NCCL / NVLink (vmn_dist_* in vermilion_b200.h) and written to Camera::mImage as for one GPU.
+        std::vector<int> devices;
+        bool splitSamples = false;
         int mode = VMN_MODE_COMPAT;      // the reference estimator; VMN_MODE_FIXED = exact spp, r2 = xi, <= maxSegments rays per path;
                                          // VMN_MODE_BRUTEFORCE = BruteForceTracer::Render (what B200BruteForceTracer sets)
         bool shadowRays = false;         // BRUTEFORCE: enable the shadow test the reference has commented out (integrators.cpp:108-110)
         uint32_t maxSegments = 5;
         uint64_t seed = 1;               // the reference seeds from std::random_device (pathtracer.cpp:231); here it is explicit
         uint64_t maxPathsInFlight = 0;   // 0 = library default
-        // multi-GPU share of the frame (one process per GPU; the caller all-reduces the film)
+        // one share of the frame rendered by this process alone (one process per GPU; the caller exchanges the film, e.g. with
+        // vmn_dist_create_rank — the in-process alternative is `devices` above)
         uint32_t tileSize = 0, tileRank = 0, tileWorld = 1;
         uint32_t sampleBegin = 0, sampleEnd = 0;
         // progressive rendering with checkpoints (FIXED mode, whole sample range): the film sums are written to checkpointPath
@@ -51,25 +57,29 @@ namespace Vermilion
         ~B200PathTracer() override;
         void Render(std::vector<Vermilion::Camera*>& cameraList, MeshEngine* mEng) override;
 
-        bool ok() const { return mCtx != nullptr && mLastStatus == VMN_OK; }
+        bool ok() const { return mGroup != nullptr && mLastStatus == VMN_OK; }
         const std::string& lastError() const { return mLastError; }
-        const vmn_stats& stats() const { return mStats; }
-        vmn_ctx* context() { return mCtx; }
+        const vmn_stats& stats() const { return mStats; }            // of devices[0]; rays_traced summed over all devices
+        const vmn_dist_stats& groupStats() const { return mGroupStats; }
+        vmn_ctx* context() { return mGroup ? vmn_dist_context(mGroup, 0) : nullptr; }
+        // The GPU copy of the scene is keyed on the CONTENT of what Render uploads (vertex, normal, uv and texture data), so an edit of
+        // the MeshEngine is picked up by the next Render without any call; invalidate() only forces the next Render to upload again.
+        void invalidate() { mSceneHash = 0; mHaveScene = false; }
 
     private:
         bool uploadScene(MeshEngine* mEng);
         bool renderProgressive(const vmn_camera& vc);
         bool fail(const char* what);
+        uint64_t frameFingerprint(const vmn_camera& vc) const;
 
         B200Options mOpt;
-        vmn_ctx* mCtx = nullptr;
+        vmn_dist* mGroup = nullptr;
         vmn_status mLastStatus = VMN_OK;
         std::string mLastError;
         vmn_stats mStats{};
-        // scene cache key: re-upload only when the MeshEngine's geometry changed
-        const void* mSceneKey = nullptr;
-        uint64_t mSceneFaces = 0;
-        size_t mSceneTextures = 0;
+        vmn_dist_stats mGroupStats{};
+        uint64_t mSceneHash = 0; // content hash of the uploaded scene
+        bool mHaveScene = false;
     };
 
     // Drop-in for `new BruteForceTracer()` (integrators.h:18-21): same adapter, VMN_MODE_BRUTEFORCE. boundTextures[0] is the

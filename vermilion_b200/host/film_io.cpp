@@ -73,10 +73,21 @@ int vmnh_save_frame(const char* name, const uint8_t* rgba, const float* depth, u
     return rc;
 }
 
+uint64_t vmnh_hash64(const void* data, uint64_t bytes, uint64_t seed) {
+    const unsigned char* p = static_cast<const unsigned char*>(data);
+    uint64_t h = seed ^ (bytes * 0x9E3779B97F4A7C15ull);
+    auto mix = [&h](uint64_t w) { h ^= w; h *= 0xFF51AFD7ED558CCDull; h ^= h >> 32; };
+    uint64_t i = 0;
+    for (; i + 8 <= bytes; i += 8) { uint64_t w; memcpy(&w, p + i, 8); mix(w); }
+    if (i < bytes) { uint64_t w = 0; memcpy(&w, p + i, bytes - i); mix(w); }
+    h ^= h >> 29; h *= 0xC4CEB9FE1A85EC53ull; h ^= h >> 32;
+    return h;
+}
+
 int vmnh_checkpoint_save(const char* path, const float* film, const vmnh_checkpoint_header* hdr) {
     if (!path || !film || !hdr || !hdr->width || !hdr->height) return 1;
     vmnh_checkpoint_header h = *hdr;
-    memcpy(h.magic, "VMNFILM1", 8);
+    memcpy(h.magic, "VMNFILM2", 8);
     const size_t bytes = (size_t)h.width * h.height * 16;
     uLong crc = crc32(0L, Z_NULL, 0);
     for (size_t off = 0; off < bytes; off += (1u << 30)) { // zlib takes 32-bit lengths
@@ -102,7 +113,7 @@ int vmnh_checkpoint_info(const char* path, vmnh_checkpoint_header* out) {
     long size = -1;
     if (ok && fseek(f, 0, SEEK_END) == 0) size = ftell(f);
     fclose(f);
-    if (!ok || memcmp(h.magic, "VMNFILM1", 8) != 0) return 2;
+    if (!ok || memcmp(h.magic, "VMNFILM2", 8) != 0) return 2;
     if (size < 0 || (uint64_t)size != sizeof(h) + (uint64_t)h.width * h.height * 16) return 2;
     *out = h;
     return 0;

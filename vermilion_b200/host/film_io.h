@@ -21,14 +21,19 @@ int vmnh_write_pfm(const char* path, const float* data, uint32_t width, uint32_t
 int vmnh_save_frame(const char* name, const uint8_t* rgba, const float* depth, uint32_t width, uint32_t height);
 
 typedef struct {
-    char magic[8];        /* "VMNFILM1" */
+    char magic[8];        /* "VMNFILM2" */
     uint32_t width, height;
     uint32_t spp_done;    /* samples [0, spp_done) of the sequence are in the film */
     uint32_t spp_total;   /* the camera's uSamplesPerPixel (fixes the stratum length spp/4) */
     uint64_t seed;        /* Philox key */
     uint32_t max_segments;
     uint32_t crc32;       /* of the payload */
+    uint64_t frame_fingerprint; /* what the film is a picture OF: camera pose and film geometry, estimator, scene and texture content
+                                 * (vmnh_hash64 chain computed by the caller, b200_pathtracer.cpp); a resume requires equality */
 } vmnh_checkpoint_header;
+
+/* 64-bit content hash (multiply-xorshift over 8-byte words, seeded; not cryptographic): scene cache key and checkpoint fingerprint */
+uint64_t vmnh_hash64(const void* data, uint64_t bytes, uint64_t seed);
 
 /* film_sum: width*height*4 floats (VMN_FILM_SUM layout). Written to <path>.tmp and renamed, so a crash never leaves a torn file. */
 int vmnh_checkpoint_save(const char* path, const float* film_sum, const vmnh_checkpoint_header* hdr);

@@ -37,6 +37,8 @@ void usage() {
             "  --camera x,y,z,rx,ry,rz            position and rotation in degrees (default -4000,1600,8000,0,25,0)\n"
             "  --film dist,sx,sy                  film distance and size (default 6,3.6,2.4)\n"
             "  --mode compat|fixed  --seed S  --segments K  --shadow   (b200 engines only)\n"
+            "  --gpus N | --devices a,b,...       (b200 engines) render the frame on several GPUs of this node: one Render call, the film\n"
+            "                                     assembled on the first device over NCCL / NVLink; --split tiles|samples (default tiles)\n"
             "  --quiet                            drop the reference's per-pixel stderr chatter (pathtracer.cpp:229)\n");
 }
 
@@ -76,6 +78,9 @@ int main(int argc, char** argv) {
         else if (a == "--segments") opt.maxSegments = (uint32_t)strtoul(value(), nullptr, 10);
         else if (a == "--spp") vcs.raysPerPixel = (uint32_t)strtoul(value(), nullptr, 10);
         else if (a == "--shadow") opt.shadowRays = true;
+        else if (a == "--gpus") { int n = atoi(value()); if (n < 1 || n > 16) { usage(); return 1; } opt.devices.clear(); for (int d = 0; d < n; ++d) opt.devices.push_back(d); }
+        else if (a == "--devices") { opt.devices.clear(); const char* p = value(); while (*p) { char* e = nullptr; long d = strtol(p, &e, 10); if (e == p) { usage(); return 1; } opt.devices.push_back((int)d); p = (*e == ',') ? e + 1 : e; } }
+        else if (a == "--split") { std::string v = value(); if (v == "samples") opt.splitSamples = true; else if (v == "tiles") opt.splitSamples = false; else { usage(); return 1; } }
         else if (a == "--quiet") quiet = true;
         else if (a == "--res") { unsigned w = 0, h = 0; if (sscanf(value(), "%ux%u", &w, &h) != 2 || !w || !h) { usage(); return 1; } vcs.imageResX = w; vcs.imageResY = h; }
         else if (a == "--camera") { float f[6]; if (!parse_floats(value(), f, 6)) { usage(); return 1; }
@@ -137,7 +142,14 @@ int main(int argc, char** argv) {
     }
     printf("{\"engine\": \"%s\", \"triangles\": %llu, \"width\": %u, \"height\": %u, \"spp\": %u, \"render_s\": %.6f, \"mean_depth_plane\": %.4f",
            engine.c_str(), (unsigned long long)nFaces, cam->uImageU, cam->uImageV, cam->uSamplesPerPixel, seconds, mean_depth / (double)np);
-    if (b200) printf(", \"rays_traced\": %llu", (unsigned long long)b200->stats().rays_traced);
+    if (b200) {
+        printf(", \"rays_traced\": %llu, \"gpus\": %u", (unsigned long long)b200->stats().rays_traced, b200->groupStats().world ? b200->groupStats().world : 1u);
+        if (b200->groupStats().world > 1) {
+            printf(", \"frame_ms\": %.3f, \"collective_ms\": %.3f, \"render_ms\": [", b200->groupStats().frame_ms, b200->groupStats().collective_ms);
+            for (uint32_t i = 0; i < b200->groupStats().local; ++i) printf("%s%.3f", i ? ", " : "", b200->groupStats().render_ms[i]);
+            printf("]");
+        }
+    }
     printf(", \"out\": \"%s.png\"}\n", out.c_str());
 
     // main.cpp:98-100
