@@ -6,7 +6,9 @@ procedural tessellated-sphere scene, 983 040 triangles, 1920x1080, 64 spp, prima
 
 A step = one full frame through the wavefront (raygen -> 5 x (extend, shade) -> accumulate per sample batch).
 N > 1 (torchrun, one rank per GPU): sample-slice split — every rank renders the full frame for its own 64-sample
-slice of an N*64-spp frame (weak scaling), then the film sums are all-reduced with NCCL inside the timed region.
+slice of an N*64-spp frame (weak scaling); the film sums are reduced to rank 0 over NCCL inside the timed region by the
+library's own multi-GPU layer (vmn_dist_*, csrc/dist.cu: the same C++ path the Integrator adapter uses). The N > 1 line also
+carries `strong`: the SAME 64-spp C2 frame split over the N GPUs (interleaved tiles + gather, and sample slices + reduce).
 `value`   device-timed, scene resident in HBM.            `e2e`  through the C ABI with host buffers: scene upload
 + GPU BVH build + render + image read-back every step.    `roofline`  for the dominant kernel (k_extend).
 `cpu_baseline` / --impl reference: the reference's own CPU code (oracle/_ref, -Ofast as shipped) on the host cores.
@@ -179,7 +181,6 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from vermilion_b200 import distributed as vd
     from vermilion_b200 import engine
 
     rank = int(os.environ.get("RANK", "0"))
@@ -203,25 +204,38 @@ def main():
     spp_total = args.spp * world
     cam = make_camera(width, height, spp_total)
     npix = width * height
+    dev = torch.device("cuda", local)
 
     def new_engine(counters=False):
         e = engine.Engine(device=local, counters=counters, max_paths=args.max_paths, stream=stream.cuda_stream)
         return e
 
-    eng = new_engine()
-    eng.set_scene(pos, nrm, uv)
-    eng.set_camera(cam)
-    d_film, n_floats = eng.film_device()
-    film_t = vd.device_film_tensor(eng, torch.device("cuda", local)) if world > 1 else None
-
-    share = vd.render_params("sample", rank, world, spp_total)  # this rank's slice of the sample sequence
-    s0, s1 = share["sample_begin"], share["sample_end"]
+    # N = 1: one context. N > 1: a rank group of the library's multi-GPU layer (one member per process; rank 0's NCCL id is handed to
+    # the others over torch.distributed, which is used for nothing else on the data path)
+    grp = None
+    if world > 1:
+        uid = torch.zeros(engine.DIST_ID_BYTES, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid.copy_(torch.tensor(list(engine.DistGroup.unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        grp = engine.DistGroup.rank(bytes(uid.cpu().tolist()), rank, world, device=local, max_paths=args.max_paths, stream=stream.cuda_stream)
+        grp.set_scene(pos, nrm, uv)
+        grp.set_camera(cam)
+        eng = None
+    else:
+        eng = new_engine()
+        eng.set_scene(pos, nrm, uv)
+        eng.set_camera(cam)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def step():
-        eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
-        if world > 1:
-            vd.reduce_film(film_t)
+        if grp is not None:
+            grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=engine.DIST_SPLIT_SAMPLES)  # 64 spp per rank + ncclReduce to rank 0
+        else:
+            eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5)
+
+    def step_stats():
+        return grp.member_stats(0) if grp is not None else eng.stats()
 
     def barrier():
         torch.cuda.synchronize()
@@ -229,32 +243,64 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed(fn, steps, warmup):
+        """`steps` calls of fn, each bracketed by CUDA events on the launching stream, L2 flushed before each; returns (sum of ms, MAX
+        over ranks) and the per-step stats"""
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        stats = []
+        for a, b in ev:
+            flush.zero_()
+            if world > 1:
+                dist.barrier()  # every rank starts the step together: the collective inside must not absorb a late starter's skew
+            a.record(stream)
+            fn()
+            b.record(stream)
+            b.synchronize()
+            stats.append(step_stats())
+        barrier()
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), stats
+
     for _ in range(args.warmup):
         step()
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    rays = extend_ms = launches = 0
-    for a, b in ev:
-        flush.zero_()
-        a.record(stream)
-        step()
-        b.record(stream)
-        b.synchronize()
-        st = eng.stats()
-        rays += st["rays_traced"]; extend_ms += st["extend_ms"]; launches += st["kernel_launches"]
-    barrier()
+    ms, sts = timed(step, args.steps, 0)
     clocks = sampler.stop() if sampler else None
-    ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([ms, float(rays), extend_ms], dtype=torch.float64, device="cuda")
+    rays = sum(st["rays_traced"] for st in sts)
+    extend_ms = sum(st["extend_ms"] for st in sts)
+    launches = sum(st["kernel_launches"] for st in sts)
+    t = torch.tensor([float(rays)], dtype=torch.float64, device=dev)
     if world > 1:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms, rays_all = float(tmax[0]), float(tsum[1])
-    else:
-        rays_all = float(rays)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    rays_all = float(t[0])
     value = rays_all / (ms / 1e3) / 1e6
     paths_all = float(npix) * args.spp * world * args.steps
+
+    # ---- strong scaling (N > 1): the SAME 64-spp frame over N GPUs, through the same group ----
+    strong = None
+    if grp is not None:
+        grp.set_camera(make_camera(width, height, args.spp))
+        strong = {"workload": f"the {args.spp}-spp C2 frame split over {world} GPUs (total work fixed)", "single_gpu_ms_per_frame": ms / args.steps,
+                  "single_gpu_note": "= ms_per_step of the weak line: there every rank renders this whole frame"}
+        for name, split in (("tiles", engine.DIST_SPLIT_TILES), ("samples", engine.DIST_SPLIT_SAMPLES)):
+            fn = lambda: grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=split)
+            sms, ssts = timed(fn, args.steps, args.warmup)
+            mine = torch.tensor([sum(st["total_ms"] for st in ssts) / args.steps], dtype=torch.float64, device=dev)
+            allr = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            per_rank = [float(x[0]) for x in allr]
+            coll = grp.stats()["collective_ms"]
+            strong[name] = {"ms_per_frame": sms / args.steps, "efficiency": (ms / args.steps) / (world * (sms / args.steps)),
+                            "render_ms_per_rank": per_rank, "slowest_rank_ms": max(per_rank), "imbalance": max(per_rank) / (sum(per_rank) / world),
+                            "assembly_ms_root_last_frame": coll,
+                            "exchange": "ncclSend/ncclRecv of each rank's own tiles (1/N of the film) to rank 0" if name == "tiles" else "ncclReduce(sum) of the film to rank 0"}
+        grp.set_camera(cam)
 
     # ---- e2e: host buffers through the C ABI, every step: scene upload + BVH build + render + image read-back ----
     ppos = torch.from_numpy(pos).pin_memory().numpy(); pnrm = torch.from_numpy(nrm).pin_memory().numpy(); puv = torch.from_numpy(uv).pin_memory().numpy()
@@ -264,15 +310,19 @@ def main():
     t0 = time.perf_counter()
     e2e_rays = 0
     for _ in range(e2e_steps):
-        eng.set_scene(ppos, pnrm, puv)
-        eng.set_camera(cam)
-        eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, sample_begin=s0, sample_end=s1)
-        if world > 1:
-            vd.reduce_film(film_t)
-            img = eng.resolve_device(d_film, out=pimg)
+        if grp is not None:
+            # the scene goes up once, on rank 0's PCIe link, and crosses NVLink to the other ranks; only rank 0 reads the image back
+            root = rank == 0
+            grp.set_scene(ppos if root else None, pnrm if root else None, puv if root else None, broadcast=True)
+            grp.set_camera(cam)
+            grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=engine.DIST_SPLIT_SAMPLES)
+            grp.read_image(out=pimg)
         else:
-            img = eng.read_image(out=pimg)
-        e2e_rays += eng.stats()["rays_traced"]
+            eng.set_scene(ppos, pnrm, puv)
+            eng.set_camera(cam)
+            eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5)
+            eng.read_image(out=pimg)
+        e2e_rays += step_stats()["rays_traced"]
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
@@ -281,15 +331,19 @@ def main():
         b = te.clone(); dist.all_reduce(b, op=dist.ReduceOp.SUM)
         e2e_s, e2e_rays = float(a[0]), float(b[1])
     e2e = {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(pos.nbytes + nrm.nbytes + uv.nbytes + 8 * 64 + 48),
-           "d2h_bytes_per_step": int(img.nbytes), "steps": e2e_steps,
-           "includes": "vmn_scene_set_triangles (H2D from pinned host) + vmn_scene_commit (GPU BVH build) + vmn_render + vmn_read_image (D2H)"}
-    build_ms = eng.stats()["build_ms"]
+           "d2h_bytes_per_step": int(pimg.nbytes), "steps": e2e_steps,
+           "includes": "vmn_scene_set_triangles (H2D from pinned host) + vmn_scene_commit (GPU BVH build) + vmn_render + vmn_read_image (D2H)" if grp is None else
+                       "vmn_dist_scene_set_triangles (H2D on rank 0 + ncclBroadcast) + vmn_dist_scene_commit (every GPU builds its BVH) + vmn_dist_render "
+                       "(64 spp per rank + ncclReduce to rank 0) + vmn_dist_read_image (D2H on rank 0 only)"}
+    build_ms = step_stats()["build_ms"]
 
     if rank != 0:
-        eng.close()
-        if world > 1:
-            dist.destroy_process_group()
+        grp.close()
+        dist.destroy_process_group()
         return
+    if grp is not None:  # rank 0 of an N > 1 run: the roofline of k_extend and the L2 probe use a plain context on this device
+        eng = new_engine()
+        eng.set_scene(pos, nrm, uv)
 
     # ---- roofline of the dominant kernel: measured visits per ray from a counting build on the same frame (untimed) ----
     ce = new_engine(counters=True)
@@ -358,12 +412,15 @@ def main():
     out = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": WORKLOAD, "resolution": f"{width}x{height}", "spp_per_gpu": args.spp, "spp_total": spp_total,
-                      "parallelism": f"sample-slice x{world} + NCCL all-reduce of the film" if world > 1 else "single GPU",
+                      "parallelism": f"sample-slice x{world} + ncclReduce of the film to rank 0 (vmn_dist)" if world > 1 else "single GPU",
                       "l2": "256 MiB L2 flush between timed steps", "paths_in_flight": args.max_paths},
            "spp_per_s": paths_all / npix / (ms / 1e3), "rays_per_step": rays_all / args.steps, "bvh_build_ms": build_ms,
-           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_c3": roofline_c3, "cpu_baseline": cpu}
+           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_c3": roofline_c3, "strong": strong,
+           "cpu_baseline": cpu}
     if eng is not None:
         eng.close()
+    if grp is not None:
+        grp.close()
     if world > 1:
         dist.destroy_process_group()
     sys.stdout.flush()
