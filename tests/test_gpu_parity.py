@@ -358,3 +358,34 @@ def test_signed_zero_direction_components_match_oracle(eng, flags):
     assert c["bad"] == 0, c
     assert c["tie"] + c["edge"] <= 0.01 * n, c  # rays through triangle centroids of a closed mesh rarely graze an edge
     assert c["hits"] > 0.9 * n and c["t_exact"] == c["hits"], c
+
+
+@pytest.mark.parametrize("textured", [False, True])
+def test_one_launch_frames_equal_the_wavefront_bit_for_bit(monkeypatch, textured):
+    """COMPAT and BRUTEFORCE frames of up to 4 Mi pixels run as ONE kernel (k_mega_compat / k_mega_bf: the pixel loop, the early-out and
+    the path loop in registers, no host round trips); larger ones, or VMN_MEGA=0, go through the wavefront stages. Both share the
+    arithmetic (raycast_finish, radiance_bounce, bf_*), so films, sample counts and ray counts must be identical — with tiles, shadow
+    rays and textures too."""
+    pos, nrm, uv = scenes.spheres(2, 2, 3, 150.0)
+    rng = np.random.default_rng(5)
+    tex = (rng.random((8, 8, 3), dtype=np.float32) - np.float32(0.5)) * np.float32(0.6) if textured else None
+    tex1 = rng.random((16, 8, 4), dtype=np.float32) if textured else None
+    cam = engine.camera_from_settings(160, 120, (0.0, 500.0, 1900.0), (0.0, 5.0, 0.0), 6.0, (3.6, 2.7), 16)
+    out = {}
+    with engine.Engine(device=0, max_paths=1 << 16) as e:  # a small pool: the wavefront path runs in several chunks
+        e.set_scene(pos, nrm, uv, texture=tex, texture1=tex1)
+        e.set_camera(cam)
+        for mega in ("1", "0"):
+            monkeypatch.setenv("VMN_MEGA", mega)
+            for name, kw in (("compat", dict(mode=engine.MODE_COMPAT)), ("compat_tiles", dict(mode=engine.MODE_COMPAT, tile_size=32, tile_rank=1, tile_world=3)),
+                             ("bf", dict(mode=engine.MODE_BRUTEFORCE)), ("bf_shadow", dict(mode=engine.MODE_BRUTEFORCE, shadow=True)),
+                             ("bf_tiles", dict(mode=engine.MODE_BRUTEFORCE, tile_size=32, tile_rank=2, tile_world=3))):
+                e.render(seed=7, **kw)
+                st = e.stats()
+                out[(name, mega)] = (e.read_image().copy(), e.read_image(engine.FILM_SUM).copy(), st["rays_traced"], st["paths_traced"], st["kernel_launches"])
+    for name in ("compat", "compat_tiles", "bf", "bf_shadow", "bf_tiles"):
+        a, b = out[(name, "1")], out[(name, "0")]
+        assert np.array_equal(a[0].view(np.uint32), b[0].view(np.uint32)), name
+        assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), name
+        assert a[2] == b[2] and a[3] == b[3], (name, a[2:], b[2:])
+        assert a[4] == 1 and b[4] > 10

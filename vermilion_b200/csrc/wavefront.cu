@@ -194,6 +194,63 @@ __device__ __forceinline__ V3 diffuse_dir(V3 N, V3 rDir, float c1, float s1, flo
     return normalize(u * c1 * r2s + v * s1 * r2s + w * sq);
 }
 
+// The part of one Radiance() iteration (pathtracer.cpp:54-196) that follows the emission bookkeeping: roulette / segment cap, the Philox
+// block of this bounce, texture lookup, mirror or diffuse continuation. Shared by the wavefront stage (k_shade) and the one-launch kernels
+// for small frames (k_mega_compat), so that both produce the same bits. `segs` is the 1-based index of this iteration (already
+// incremented); pixel_of(&pixel, &sample) names the Philox stream and is only evaluated for a path that is still alive.
+template <class PixelOf>
+__device__ __forceinline__ bool radiance_bounce(const SceneDev& sc, int mode, uint32_t max_segments, uint64_t seed, const RayCastOut& h, V3 rDir,
+                                                uint32_t& depth, uint32_t segs, float4& tp, bool& thr_dirty, V3* nStart_out, V3* nDir_out, PixelOf pixel_of) {
+    bool alive = true;
+    V3 nStart(0, 0, 0), nDir(0, 0, 0);
+    uint64_t pixel; uint32_t sample;
+    pixel_of(&pixel, &sample);
+    // iteration `segs` of the path draws from Philox block `segs` (block 0 holds the two pixel jitters): one block per bounce,
+    // generated once by every lane that still needs numbers; at most four are used (roulette, mirror test, two angles)
+    BounceRng rng;
+    if (mode == VMN_MODE_FIXED) {
+        ++depth;
+        if (segs >= max_segments) alive = false;
+        else rng.init(seed, pixel, sample, segs);
+    } else {
+        ++depth;
+        rng.init(seed, pixel, sample, segs);
+        if (depth > 5 && (rng.next01() > 0.95f || depth > 1000)) alive = false; // :56-59
+    }
+    if (alive) {
+        const float r2scale = (mode == VMN_MODE_FIXED) ? 1.f : 10.f;
+        float sc4[4] = {1.f, 1.f, 1.f, 1.f};
+        if (h.material && sc.tex) texture_sample(sc, h.uv0, h.uv1, sc4); // :62-80
+        if (h.material && rng.next01() >= 0.96) { // mirror :98-109 (its three unused noise draws need no numbers)
+            nStart = h.P - rDir * 0.001f;
+            nDir = normalize(rDir - h.N * 2.f * dot(h.N, rDir));
+        } else {
+            // diffuse off a triangle (:151-165) or off a sphere (:166-190): the two branches differ in where the draws are narrowed
+            // to float, and share one sincos + hemisphere frame (a warp almost always holds both kinds of hit)
+            const double xi1 = rng.next01(), xi2 = rng.next01();
+            double r1d;
+            float r2s, sq;
+            if (h.material) {
+                if (sc.tex) { tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3]; thr_dirty = true; } // without a texture: * 1
+                const float r1 = (float)(2 * 3.14159265358979323846 * xi1);
+                const float r2 = (float)((double)r2scale * xi2);
+                r2s = sqrtf(r2); sq = sqrtf(1 - r2);
+                r1d = (double)r1; // cos(r1), sin(r1) of pathtracer.cpp:160 take the float r1 promoted to double
+            } else {
+                r1d = 2 * 3.14159265358979323846 * xi1;
+                const double r2 = (double)r2scale * xi2;
+                r2s = (float)sqrt(r2); sq = (float)sqrt(1 - r2); // (:172-174 draw three unused numbers)
+            }
+            double s1, c1;
+            sincos(r1d, &s1, &c1);
+            nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, sq);
+            nStart = h.P - rDir * 0.001f;
+        }
+    }
+    *nStart_out = nStart; *nDir_out = nDir;
+    return alive;
+}
+
 // One iteration of Radiance()'s loop (pathtracer.cpp:36-196) for every queued ray.
 #ifndef VMN_SHADE_MINB
 #define VMN_SHADE_MINB 9 // 56 registers: nine 128-thread CTAs per SM (8 -> 9: shade -1.3 %; 10 spills)
@@ -240,60 +297,15 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             } else if (depth == 0) {
                 radiance[slot] = make_float4(0.f, 0.f, 0.f, -100.f); // a primary ray that leaves the scene (:37-41 returns the initial value)
             }
-            if (alive) {
-                // pixel/sample of this slot (Philox counter)
-                uint64_t pixel; uint32_t sample;
-                if (radiance_query) { pixel = slot; sample = 0; }
-                else {
+            if (alive)
+                alive = radiance_bounce(sc, rp.mode, rp.max_segments, rp.seed, h, rDir, depth, segs, tp, thr_dirty, &nStart, &nDir, [&](uint64_t* pixel, uint32_t* sample) {
+                    if (radiance_query) { *pixel = slot; *sample = 0; return; }
                     // slot = k * n_local + lp with a 32-bit slot: one 32-bit divide (a 64-bit one was 4 % of this kernel's instructions)
                     uint32_t k = 0, lp = slot;
                     if ((rp.n_local >> 32) == 0) { k = slot / (uint32_t)rp.n_local; lp = slot - k * (uint32_t)rp.n_local; }
-                    map_pixel(pm, rp.lp0 + lp, &pixel);
-                    sample = rp.s0 + k;
-                }
-                // iteration `segs` of the path draws from Philox block `segs` (block 0 holds the two pixel jitters): one block per bounce,
-                // generated once by every lane that still needs numbers; at most four are used (roulette, mirror test, two angles)
-                BounceRng rng;
-                if (rp.mode == VMN_MODE_FIXED) {
-                    ++depth;
-                    if (segs >= rp.max_segments) alive = false;
-                    else rng.init(rp.seed, pixel, sample, segs);
-                } else {
-                    ++depth;
-                    rng.init(rp.seed, pixel, sample, segs);
-                    if (depth > 5 && (rng.next01() > 0.95f || depth > 1000)) alive = false; // :56-59
-                }
-                if (alive) {
-                    const float r2scale = (rp.mode == VMN_MODE_FIXED) ? 1.f : 10.f;
-                    float sc4[4] = {1.f, 1.f, 1.f, 1.f};
-                    if (h.material && sc.tex) texture_sample(sc, h.uv0, h.uv1, sc4); // :62-80
-                    if (h.material && rng.next01() >= 0.96) { // mirror :98-109 (its three unused noise draws need no numbers)
-                        nStart = h.P - rDir * 0.001f;
-                        nDir = normalize(rDir - h.N * 2.f * dot(h.N, rDir));
-                    } else {
-                        // diffuse off a triangle (:151-165) or off a sphere (:166-190): the two branches differ in where the draws are narrowed
-                        // to float, and share one sincos + hemisphere frame (a warp almost always holds both kinds of hit)
-                        const double xi1 = rng.next01(), xi2 = rng.next01();
-                        double r1d;
-                        float r2s, sq;
-                        if (h.material) {
-                            if (sc.tex) { tp.x *= sc4[0]; tp.y *= sc4[1]; tp.z *= sc4[2]; tp.w *= sc4[3]; thr_dirty = true; } // without a texture: * 1
-                            const float r1 = (float)(2 * 3.14159265358979323846 * xi1);
-                            const float r2 = (float)((double)r2scale * xi2);
-                            r2s = sqrtf(r2); sq = sqrtf(1 - r2);
-                            r1d = (double)r1; // cos(r1), sin(r1) of pathtracer.cpp:160 take the float r1 promoted to double
-                        } else {
-                            r1d = 2 * 3.14159265358979323846 * xi1;
-                            const double r2 = (double)r2scale * xi2;
-                            r2s = (float)sqrt(r2); sq = (float)sqrt(1 - r2); // (:172-174 draw three unused numbers)
-                        }
-                        double s1, c1;
-                        sincos(r1d, &s1, &c1);
-                        nDir = diffuse_dir(h.N, rDir, (float)c1, (float)s1, r2s, sq);
-                        nStart = h.P - rDir * 0.001f;
-                    }
-                }
-            }
+                    map_pixel(pm, rp.lp0 + lp, pixel);
+                    *sample = rp.s0 + k;
+                });
             if (thr_dirty) thr[slot] = tp;
             mt_out = (depth & 0x7FFFu) | ((thr_written || thr_dirty) ? kThrWritten : 0u) | (segs << 16);
             if (!alive && radiance_query) meta[slot] = mt_out; // vmn_radiance reports the segments of each finished path
@@ -605,6 +617,9 @@ vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* ou
     return VMN_OK;
 }
 
+static bool mega_wanted(uint64_t n_local);
+static vmn_status render_mega(vmn_ctx* c, const vmn_render_params* prm, const PixelMap& pm, uint64_t n_local);
+
 vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     const uint64_t npix = c->film_pixels;
     const uint32_t spp = c->cam.spp;
@@ -623,6 +638,10 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     if ((prm->flags & VMN_RENDER_ACCUMULATE) && mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "VMN_RENDER_ACCUMULATE needs VMN_MODE_FIXED");
     if (!(prm->flags & VMN_RENDER_ACCUMULATE)) VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
     if (n_local_total == 0 || s_begin == s_end) return VMN_OK;
+    if (mode == VMN_MODE_COMPAT && mega_wanted(n_local_total)) {
+        if (spp / 4 == 0) return VMN_OK; // spp < 4: the reference takes no samples at all
+        return render_mega(c, prm, pm, n_local_total);
+    }
 
     // queue slots and counts are 32-bit: never more than 2^32 - 16 paths in flight, whatever max_paths says
     const uint64_t cap = c->max_paths < 0xFFFFFFF0ull ? c->max_paths : 0xFFFFFFF0ull;
@@ -792,11 +811,9 @@ __device__ __forceinline__ float abs_via_int(float x) {
 }
 
 // the end of one sample of pixel `lp` (integrators.cpp:141-173) and, when the pixel stops, its film entry (:176-183)
-__device__ __forceinline__ void bf_finish_sample(const SceneDev& sc, const PixelMap& pm, const BfParams& bp, uint32_t lp, bool hit, float vNDL, float u,
-                                                 float v, float dist, float4* __restrict__ accum_a, float4* __restrict__ last_a,
-                                                 uint2* __restrict__ meta_a, float4* __restrict__ film, float2* __restrict__ aux) {
-    float4 accum = accum_a[lp], last = last_a[lp];
-    const uint32_t n = meta_a[lp].x + 1u; // ++nTotalSamples (:63)
+// the end of one sample (integrators.cpp:141-173) on register state: adds the sample, runs the early-out; true = the pixel stops
+__device__ __forceinline__ bool bf_sample_end(const SceneDev& sc, uint32_t spp, bool hit, float vNDL, float u, float v, float4& accum, float4& last,
+                                              uint32_t n /* nTotalSamples after ++ (:63) */) {
     if (hit) {
         float4 cur;
         if (sc.tex1) { // :141-147
@@ -815,15 +832,42 @@ __device__ __forceinline__ void bf_finish_sample(const SceneDev& sc, const Pixel
         if (abs_via_int(last.x + last.y + last.z + last.w) < 0.001f) done = true;
     }
     if (!done) last = make_float4(accum.x / fn, accum.y / fn, accum.z / fn, accum.w / fn); // :173
-    if (n >= bp.spp) done = true;
+    if (n >= spp) done = true;
+    return done;
+}
+
+// the end of one sample of pixel `lp` and, when the pixel stops, its film entry (:176-183)
+__device__ __forceinline__ void bf_finish_sample(const SceneDev& sc, const PixelMap& pm, const BfParams& bp, uint32_t lp, bool hit, float vNDL, float u,
+                                                 float v, float dist, float4* __restrict__ accum_a, float4* __restrict__ last_a,
+                                                 uint2* __restrict__ meta_a, float4* __restrict__ film, float2* __restrict__ aux) {
+    float4 accum = accum_a[lp], last = last_a[lp];
+    const uint32_t n = meta_a[lp].x + 1u; // ++nTotalSamples (:63)
+    const bool done = bf_sample_end(sc, bp.spp, hit, vNDL, u, v, accum, last, n);
     accum_a[lp] = accum; last_a[lp] = last; meta_a[lp] = make_uint2(n, done ? 1u : 0u);
     if (done) {
         uint64_t pixel;
         if (map_pixel(pm, bp.lp0 + lp, &pixel)) {
-            film[pixel] = make_float4(accum.x, accum.y, accum.z, fn);
+            film[pixel] = make_float4(accum.x, accum.y, accum.z, (float)n);
             aux[pixel] = make_float2(accum.w, dist);
         }
     }
+}
+
+// integrators.cpp:83-119 for a primary hit: light direction, N.L (with the normal map of texture slot 0), mirror-probe direction
+__device__ __forceinline__ void bf_primary_shade(const SceneDev& sc, const RayCastOut& h, float* vNDL_out, V3* sdir, V3* ldir_out) {
+    const V3 lightLocation(500.f, 1100.f, 2000.f); // :16
+    const V3 ldir = normalize(lightLocation - h.P); // :83-84
+    V3 hn = h.N;
+    float vNDL = dot(ldir, normalize(hn)); // :88
+    if (sc.tex) { // :98-106
+        float n4[4];
+        texture_sample(sc, h.uv0, h.uv1, n4);
+        hn = hn + V3(n4[0], n4[1], n4[2]);
+        vNDL = dot(ldir, normalize(hn));
+    }
+    const V3 nl = -ldir;
+    *sdir = nl - (hn * 2.f) * dot(hn, nl); // :119
+    *vNDL_out = vNDL; *ldir_out = ldir;
 }
 
 __global__ void __launch_bounds__(kWfBlock) k_bf_shade1(SceneDev sc, const SphereDev* __restrict__ sph, PixelMap pm, BfParams bp,
@@ -849,18 +893,8 @@ __global__ void __launch_bounds__(kWfBlock) k_bf_shade1(SceneDev sc, const Spher
             if (!h.hit) {
                 bf_finish_sample(sc, pm, bp, slot, false, 0.f, 0.f, 0.f, h.dist, accum, last, meta, film, aux); // :160-164
             } else {
-                const V3 lightLocation(500.f, 1100.f, 2000.f); // :16
-                ldir = normalize(lightLocation - h.P); // :83-84
-                V3 hn = h.N;
-                float vNDL = dot(ldir, normalize(hn)); // :88
-                if (sc.tex) { // :98-106
-                    float n4[4];
-                    texture_sample(sc, h.uv0, h.uv1, n4);
-                    hn = hn + V3(n4[0], n4[1], n4[2]);
-                    vNDL = dot(ldir, normalize(hn));
-                }
-                const V3 nl = -ldir;
-                sdir = nl - (hn * 2.f) * dot(hn, nl); // :119
+                float vNDL;
+                bf_primary_shade(sc, h, &vNDL, &sdir, &ldir);
                 P = h.P;
                 tmp[slot] = make_float4(vNDL, h.uv0, h.uv1, h.dist);
                 emit = true;
@@ -909,6 +943,164 @@ __global__ void __launch_bounds__(kWfBlock) k_bf_shade2(SceneDev sc, const Spher
     }
 }
 
+// ---- one-launch frames -----------------------------------------------------------------------------------------------------------
+// The adaptive estimators (COMPAT PathTracer, BruteForceTracer) take a data-dependent number of samples per pixel and of rays per
+// sample, so their wavefront needs the host to read a counter after every few launches to know when to stop: C1 (512 x 512, 16 spp)
+// was 240 launches and a dozen stream synchronisations for 4.8 ms of work. For frames of up to a few million pixels the whole pixel
+// loop of pathtracer.cpp:242-324 / integrators.cpp:59-183 runs in ONE kernel instead: one thread per pixel, the sample loop, the early-out
+// state machine and the path loop in registers, the single-ray form of the same BVH8 traversal (trace_wide), the same raycast_finish /
+// radiance_bounce / bf_* code and the same Philox streams as the wavefront stages — so the film is bit-identical to the wavefront's
+// (tests run both). Divergence costs lanes, but these frames are launch-bound, not throughput-bound.
+struct MegaParams {
+    uint64_t seed, n_local;
+    uint32_t spp, per, max_segments, flags;
+};
+
+__device__ __forceinline__ uint32_t mega_trace(const SceneDev& sc, V3 o, V3 d, float* t, uint2* sstack) {
+    TravCounters cnt{0ull, 0ull};
+    return leaf_original_id(sc.tris, trace_wide<false>(sc, o, d, t, sstack, kWfBlock, &cnt));
+}
+
+__global__ void __launch_bounds__(kWfBlock) k_mega_compat(SceneDev sc, const SphereDev* __restrict__ sph, CamDev cam, PixelMap pm, MegaParams mp,
+                                                          float4* __restrict__ film, unsigned long long* __restrict__ frame_ctr) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t pixel;
+    if (lp >= mp.n_local || !map_pixel(pm, lp, &pixel)) return;
+    float4 f = film[pixel];
+    uint32_t st = 0, sz = 0, rays = 0, samples = 0;
+    for (uint32_t round = 0;; ++round) { // one sample per iteration: k_raygen + (k_extend, k_shade)* + k_accumulate of the wavefront
+        Rng jr(mp.seed, pixel, round, 0);
+        const float jx = jr.jitter(), jy = jr.jitter();
+        V3 o, d;
+        camera_ray(cam, pixel, (st >> 1) & 1u, st & 1u, jx, jy, &o, &d);
+        float4 acc = make_float4(0.f, 0.f, 0.f, -100.f), tp = make_float4(1.f, 1.f, 1.f, 1.f);
+        uint32_t depth = 0, segs = 0;
+        bool thr_written = false;
+        for (bool alive = true; alive;) {
+            float t;
+            const uint32_t id = mega_trace(sc, o, d, &t, sstack);
+            ++rays;
+            const RayCastOut h = raycast_finish(sc, sph, o, d, t, id);
+            ++segs;
+            alive = h.hit; // :37-41
+            if (alive) {
+                if (thr_written || depth == 0 || h.Le.x != 0.f || h.Le.y != 0.f || h.Le.z != 0.f) { // as k_shade (x + 1*0 = x otherwise)
+                    float4 a = depth == 0 ? make_float4(0.f, 0.f, 0.f, -100.f) : acc;
+                    a.x += tp.x * h.Le.x; a.y += tp.y * h.Le.y; a.z += tp.z * h.Le.z; a.w += tp.w * 0.f; // :43
+                    if (depth == 0) a.w = h.dist; // :44-47
+                    acc = a;
+                }
+                if (length(h.Le) > 1.f) alive = false; // :52
+            } else if (depth == 0) acc = make_float4(0.f, 0.f, 0.f, -100.f);
+            if (alive) {
+                bool thr_dirty = false;
+                V3 no, nd;
+                alive = radiance_bounce(sc, VMN_MODE_COMPAT, mp.max_segments, mp.seed, h, d, depth, segs, tp, thr_dirty, &no, &nd,
+                                        [&](uint64_t* px, uint32_t* smp) { *px = pixel; *smp = round; });
+                thr_written = thr_written || thr_dirty;
+                o = no; d = nd;
+            }
+        }
+        ++samples;
+        // k_accumulate, COMPAT branch (pathtracer.cpp:282-312)
+        f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += 1.f;
+        const uint32_t n = (uint32_t)f.w;
+        bool brk = false;
+        if ((double)n > sqrt((double)mp.spp)) { // :290
+            const float fn = (float)n, fn1 = (float)(n + 1);
+            V3 a(f.x / fn, f.y / fn, f.z / fn), b((f.x + acc.x) / fn1, (f.y + acc.y) / fn1, (f.z + acc.z) / fn1);
+            if (fabsf(length(a - b)) < 0.00001f) brk = true;
+        }
+        ++sz;
+        if (brk || sz >= mp.per) { sz = 0; if (st == 3) break; ++st; }
+    }
+    film[pixel] = f;
+    atomicAdd(frame_ctr + 2, (unsigned long long)rays);
+    atomicAdd(frame_ctr + 3, (unsigned long long)samples);
+}
+
+__global__ void __launch_bounds__(kWfBlock) k_mega_bf(SceneDev sc, const SphereDev* __restrict__ sph, CamDev cam, PixelMap pm, MegaParams mp,
+                                                      float4* __restrict__ film, float2* __restrict__ aux, unsigned long long* __restrict__ frame_ctr) {
+    __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
+    uint2* sstack = sstack_all + threadIdx.x;
+    const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t pixel;
+    if (lp >= mp.n_local || !map_pixel(pm, lp, &pixel)) return;
+    float4 accum = make_float4(0.f, 0.f, 0.f, 0.f), last = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t n = 0, rays = 0;
+    float dist = 0.f;
+    for (bool done = false; !done;) {
+        Rng jr(mp.seed, pixel, n, 0); // sample index = samples taken so far
+        const float jx = jr.jitter(), jy = jr.jitter();
+        V3 o, d;
+        bf_camera_ray(cam, pixel, jx, jy, &o, &d);
+        float t;
+        uint32_t id = mega_trace(sc, o, d, &t, sstack);
+        ++rays;
+        const RayCastOut h = raycast_finish(sc, sph, o, d, t, id); // :81
+        ++n;
+        dist = h.dist;
+        if (!h.hit) { done = bf_sample_end(sc, mp.spp, false, 0.f, 0.f, 0.f, accum, last, n); continue; } // :160-164
+        float vNDL;
+        V3 sdir, ldir;
+        bf_primary_shade(sc, h, &vNDL, &sdir, &ldir);
+        id = mega_trace(sc, h.P, sdir, &t, sstack); // the mirror-direction probe (:119-121)
+        ++rays;
+        const RayCastOut h2 = raycast_finish(sc, sph, h.P, sdir, t, id);
+        if (mp.flags & VMN_RENDER_BF_SHADOW) { // :108-110 with RayCastCollision's test (meshEngine.cpp:196-207)
+            float ts;
+            const uint32_t ids = mega_trace(sc, h.P, ldir, &ts, sstack);
+            ++rays;
+            if (ids != VMN_MISS && (double)ts > 1e-3) vNDL *= 0.00f;
+        }
+        if (!h2.hit) { vNDL *= 0.9f; vNDL += 0.1f; } // :133-137
+        done = bf_sample_end(sc, mp.spp, true, vNDL, h.uv0, h.uv1, accum, last, n);
+    }
+    film[pixel] = make_float4(accum.x, accum.y, accum.z, (float)n);
+    aux[pixel] = make_float2(accum.w, dist);
+    atomicAdd(frame_ctr + 2, (unsigned long long)rays);
+    atomicAdd(frame_ctr + 3, (unsigned long long)n);
+}
+
+// VMN_MEGA=0 never, 1 always, unset: frames of up to 4 Mi pixels (1080p is 2 Mi). Read at every render (tests switch it).
+static bool mega_wanted(uint64_t n_local) {
+    const char* e = getenv("VMN_MEGA");
+    if (e && *e) return atoi(e) != 0;
+    return n_local <= (4ull << 20);
+}
+
+static vmn_status render_mega(vmn_ctx* c, const vmn_render_params* prm, const PixelMap& pm, uint64_t n_local) {
+    vmn_status s = pool_ensure(c, 0);
+    if (s != VMN_OK) return s;
+    PathPool* p = c->pool;
+    unsigned long long* ctr = reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + kOffFrame);
+    VMN_CUDA(c, cudaMemsetAsync(ctr, 0, 32, c->stream));
+    MegaParams mp{};
+    mp.seed = prm->seed; mp.n_local = n_local; mp.spp = c->cam.spp; mp.per = c->cam.spp / 4; mp.max_segments = prm->max_segments ? prm->max_segments : 5;
+    mp.flags = prm->flags;
+    const CamDev cd = cam_dev(c);
+    VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+    const uint32_t grid = cdiv64(n_local, kWfBlock);
+    if (prm->mode == VMN_MODE_BRUTEFORCE)
+        k_mega_bf<<<grid, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), cd, pm, mp, c->film.as<float4>(), c->film_aux.as<float2>(), ctr);
+    else
+        k_mega_compat<<<grid, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), cd, pm, mp, c->film.as<float4>(), ctr);
+    VMN_CUDA(c, cudaGetLastError());
+    VMN_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+    unsigned long long h[4] = {0, 0, 0, 0};
+    VMN_CUDA(c, cudaMemcpyAsync(h, ctr, 32, cudaMemcpyDeviceToHost, c->stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]);
+    c->stats.total_ms = ms; c->stats.extend_ms = ms; // one kernel: traversal and shading are not separable
+    c->stats.kernel_launches = 1;
+    c->stats.rays_traced = h[2]; c->stats.paths_traced = h[3];
+    c->stats.nodes_visited = 0; c->stats.tris_tested = 0;
+    return VMN_OK;
+}
+
 vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
     const uint64_t npix = c->film_pixels;
     const uint32_t spp = c->cam.spp;
@@ -925,6 +1117,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
     VMN_CUDA(c, cudaMemsetAsync(c->film_aux.p, 0, 8 * npix, c->stream));
     c->film_bf = true;
     if (n_local_total == 0 || spp == 0) return VMN_OK; // spp == 0: the reference divides 0 by 0; here the film stays empty
+    if (mega_wanted(n_local_total)) return render_mega(c, prm, pm, n_local_total);
 
     const uint32_t stride = (prm->flags & VMN_RENDER_BF_SHADOW) ? 2u : 1u;
     uint64_t chunk = c->max_paths / stride;
