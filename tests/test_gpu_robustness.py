@@ -57,6 +57,17 @@ def test_too_deep_tree_is_refused_at_commit_and_overflow_is_reported():
     assert out.count("INTERSECT_REPORTED") == 2 and "traversal stack overflowed" in out, out
 
 
+def test_checked_build_runs_every_kernel_without_a_bounds_violation():
+    """compute-sanitizer is closed on this GPU pool, so the library carries its own memcheck: the `checked` build (-DVMN_CHECKED=1) tests
+    every data-dependent index against its array before the access and raises VMN_DEVERR_BOUNDS -> VMN_ERR_STATE. tools/sanitize_small.py
+    drives every kernel of the library on small scenes (and compares the results with the CPU oracle)."""
+    lib = os.path.join(ROOT, "vermilion_b200", "variants", "libvermilion_b200_checked.so")
+    assert os.path.exists(lib), "variants/libvermilion_b200_checked.so missing: run __graft_entry__.build()"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sanitize_small.py")], env=dict(os.environ, VMN_LIB=lib), stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "all kernels ran" in r.stdout, r.stdout[-3000:]
+
+
 def test_render_distributed_orders_the_collective_for_a_default_stream_engine():
     import torch
     import torch.distributed as dist

@@ -66,6 +66,7 @@ static uint64_t spread21(uint64_t x) {
     x = (x | x << 4) & 0x10C30C30C30C30C3ull; x = (x | x << 2) & 0x1249249249249249ull;
     return x;
 }
+static int g_emc = 0;
 static void morton_order(const Scene& sc, std::vector<uint64_t>& keys, std::vector<uint32_t>& order) {
     const size_t n = sc.tris.size();
     keys.resize(n); order.resize(n);
@@ -80,6 +81,18 @@ static void morton_order(const Scene& sc, std::vector<uint64_t>& keys, std::vect
             q[a] = (uint64_t)std::min(f * 2097152.f, 2097151.f);
         }
         k[i] = (spread21(q[0]) << 2) | (spread21(q[1]) << 1) | spread21(q[2]);
+        if (g_emc > 0) { // extended Morton code (Vinkler, Bittner, Havran 2017): a box-size bit after every g_emc-th xyz triple
+            float dx = sc.boxes[i].hi[0] - sc.boxes[i].lo[0], dy = sc.boxes[i].hi[1] - sc.boxes[i].lo[1], dz = sc.boxes[i].hi[2] - sc.boxes[i].lo[2];
+            float ex = sc.bounds.hi[0] - sc.bounds.lo[0], ey = sc.bounds.hi[1] - sc.bounds.lo[1], ez = sc.bounds.hi[2] - sc.bounds.lo[2];
+            float diag = std::sqrt(dx * dx + dy * dy + dz * dz) / std::sqrt(ex * ex + ey * ey + ez * ez);
+            uint64_t sq = (uint64_t)std::min(diag * 1048576.f, 1048575.f); // 20 bits, large boxes first... (MSB = large)
+            uint64_t out = 0; int ob = 63, sb = 19;
+            for (int t = 20; t >= 0 && ob >= 0; --t) { // xyz triples from the top
+                for (int a = 0; a < 3 && ob >= 0; ++a) { out |= ((q[a] >> t) & 1ull) << ob; --ob; }
+                if (((20 - t) % g_emc) == g_emc - 1 && sb >= 0 && ob >= 0) { out |= ((sq >> sb) & 1ull) << ob; --ob; --sb; }
+            }
+            k[i] = out;
+        }
     }
     std::iota(order.begin(), order.end(), 0u);
     std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return k[a] < k[b]; });
@@ -606,6 +619,7 @@ int main(int argc, char** argv) {
     const std::string sspec = argv[1], rspec = argv[2], bspec = argv[3], cspec = argv[4];
     g_ideal = getenv("TL_IDEAL") && getenv("TL_IDEAL")[0] == '1';
     g_order = getenv("TL_ORDER") ? atoi(getenv("TL_ORDER")) : 0;
+    g_emc = getenv("TL_EMC") ? atoi(getenv("TL_EMC")) : 0;
     double t0 = omp_get_wtime();
     Scene sc = make_scene(sspec);
     double t1 = omp_get_wtime();

@@ -204,7 +204,11 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             // branch is unreachable for a committed scene — if it ever runs, the dropped push is REPORTED (VMN_ERR_STATE), never silent
             if (s.sp < VMN_SH_STACK) { sstack[s.sp * sstride] = s.ng; ++s.sp; }
             else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
-            else atomicOr(sc.err, VMN_DEVERR_STACK);
+            else { // report, and abandon this ray: nothing pending, nothing stacked -> trav_pop ends it
+                atomicOr(sc.err, VMN_DEVERR_STACK);
+                s.ng = make_uint2(0u, 0u); s.tg = make_uint2(0u, 0u); s.sp = 0;
+                return;
+            }
         }
         VMN_CHECK(sc.err, nidx < sc.n_wide && s.sp >= 0 && s.sp <= (int)kTravStackCap);
         const uint4* np = nodes + (uint64_t)kNodeStride16 * nidx;
@@ -285,6 +289,20 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
                 hl &= hl - 1u;
                 const uint32_t m = __byte_perm(q1.z, q1.w, j) & 0xFFu; // byte j of the 8 meta bytes
                 hitmask |= (m >> 5) << (m & 31u);
+                // out-of-cache scenes: the pooled triangle phase runs a few node steps from now; its DRAM round trip starts here
+                if (sc.ooc & VMN_OOC_PREFETCH_TRIS) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.tris + (q1.y + (m & 31u))));
+            }
+            if ((sc.ooc & VMN_OOC_PREFETCH_SIBS) && (x & (x - 1u))) {
+                // hit internal children other than the one visited next: they are popped after that child's whole subtree (tens of
+                // microseconds later, well inside the L2's residence time): fetch them into the L2 now
+                uint32_t rest = x & ~(1u << (31u - __clz(x)));
+                while (rest) {
+                    const uint32_t slot = (31u - __clz(rest)) ^ s.oct_inv;
+                    rest &= ~(1u << (31u - __clz(rest)));
+                    const uint4* sp4 = nodes + (uint64_t)kNodeStride16 * (q1.x + __popc(imask & ((1u << slot) - 1u)));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(sp4));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(sp4 + 4));
+                }
             }
         }
 #else
@@ -463,6 +481,10 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
     s.tg = make_uint2(0u, 0u);
     uint2 lstack[VMN_LOCAL_STACK];
     bool active = false, exhausted = false;
+    // s.sp == -1 marks "this lane's finished ray has not been stored yet": store() runs with the next refill, when several lanes are
+    // idle, instead of once per finishing lane (ncu, C3: the dependent loads of store() were 10.7 % of all stall samples at 1.6 active
+    // lanes, stalling the 25 lanes that were still traversing). The flag lives in the stack pointer: no extra register.
+    s.sp = 0;
     uint64_t ray = 0, wbase = 0;
     uint32_t wleft = 0; // warp-uniform: rays left in the claimed chunk [wbase, wbase + wleft)
     while (true) {
@@ -489,6 +511,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
             }
             const uint32_t need = (uint32_t)__popc(idle);
             const uint32_t take = need < wleft ? need : wleft;
+            if (!active && s.sp < 0) { store(ray, s); s.sp = 0; }
             if (!active) {
                 const uint32_t r = (uint32_t)__popc(idle & ((1u << lane) - 1u));
                 if (r < take) {
@@ -505,6 +528,7 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
             if (exhausted) break;
             continue;
         }
+        if (exhausted && !active && s.sp < 0) { store(ray, s); s.sp = 0; } // no refill will come: store as lanes finish
 #if VMN_TRI_DEFER && VMN_COOP
         if (active && s.tg.y == 0u) trav_node<COUNT>(s, sc, sstack, sstride, lstack, cnt);
 #else
@@ -517,10 +541,11 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
         if (active) trav_tris<COUNT>(s, sc, cnt);
 #endif
         if (active && s.tg.y == 0u && !trav_pop(s, sstack, sstride, lstack)) {
-            store(ray, s);
+            s.sp = -1;
             active = false;
         }
     }
+    if (!active && s.sp < 0) store(ray, s);
 }
 
 __device__ __forceinline__ uint32_t pick_chunk(uint64_t n, uint32_t warps) {
@@ -574,7 +599,7 @@ __device__ __forceinline__ uint32_t trace_bvh2(const SceneDev& sc, V3 o, V3 d, f
             const bool swap = tn[1] < tn[0];
             const int nearc = swap ? c.y : c.x, farc = swap ? c.x : c.y;
             if (sp < (int)kTravStackCap) stack[sp++] = farc;
-            else atomicOr(sc.err, VMN_DEVERR_STACK);
+            else { atomicOr(sc.err, VMN_DEVERR_STACK); break; } // report, and abandon this ray
             node = nearc;
         } else if (hit[0]) node = c.x;
         else if (hit[1]) node = c.y;

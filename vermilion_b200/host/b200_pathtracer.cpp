@@ -147,6 +147,7 @@ bool B200PathTracer::renderProgressive(const vmn_camera& vc)
     }
     const uint32_t every = mOpt.checkpointEverySpp ? mOpt.checkpointEverySpp : vc.spp;
     bool first = done == 0;
+    mProgressiveRays = 0;
     while (done < vc.spp)
     {
         vmn_render_params rp{};
@@ -158,6 +159,7 @@ bool B200PathTracer::renderProgressive(const vmn_camera& vc)
         if ((mLastStatus = vmn_dist_render(mGroup, &rp, VMN_DIST_SPLIT_SAMPLES, 0)) != VMN_OK) return fail("vmn_dist_render");
         first = false;
         done = rp.sample_end;
+        { vmn_dist_stats gs{}; vmn_dist_get_stats(mGroup, &gs); mProgressiveRays += gs.rays_traced; }
         if ((mLastStatus = vmn_dist_read_image(mGroup, film.data(), VMN_FILM_SUM)) != VMN_OK) return fail("vmn_dist_read_image");
         memcpy(h.magic, "VMNFILM2", 8);
         h.width = vc.width; h.height = vc.height; h.spp_done = done; h.spp_total = vc.spp; h.seed = mOpt.seed; h.max_segments = mOpt.maxSegments;
@@ -205,7 +207,8 @@ void B200PathTracer::Render(std::vector<Vermilion::Camera*>& cameraList, MeshEng
         }
         vmn_get_stats(root, &mStats);
         vmn_dist_get_stats(mGroup, &mGroupStats);
-        if (vmn_dist_world(mGroup) > 1 && !mOpt.tileSize && !progressive) mStats.rays_traced = mGroupStats.rays_traced;
+        if (progressive) mStats.rays_traced = mProgressiveRays; // rays of the passes this call rendered (a resumed frame: fewer)
+        else if (vmn_dist_world(mGroup) > 1 && !mOpt.tileSize) mStats.rays_traced = mGroupStats.rays_traced;
 
         const uint64_t npix = (uint64_t)vc.width * vc.height;
         if (cam->renderMode == vermRenderMode::RGBAZ)

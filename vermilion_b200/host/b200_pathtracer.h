@@ -80,6 +80,7 @@ namespace Vermilion
         vmn_dist_stats mGroupStats{};
         uint64_t mSceneHash = 0; // content hash of the uploaded scene
         bool mHaveScene = false;
+        uint64_t mProgressiveRays = 0;
     };
 
     // Drop-in for `new BruteForceTracer()` (integrators.h:18-21): same adapter, VMN_MODE_BRUTEFORCE. boundTextures[0] is the
