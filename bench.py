@@ -172,6 +172,7 @@ def main():
     ap.add_argument("--res", default="1920x1080")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-c4c5", action="store_true", help="skip the C4 / C5 records of an N > 1 run (52 M-triangle city at 4K; progressive 4K render)")
     ap.add_argument("--no-c3", action="store_true", help="skip the roofline_c3 record (10 M-triangle soup, N = 1 only)")
     ap.add_argument("--max-paths", type=int, default=32 << 20, help="paths in flight (112 B each); larger batches amortise the tail of every persistent launch")
     args = ap.parse_args()
@@ -302,6 +303,88 @@ def main():
                             "exchange": "ncclSend/ncclRecv of each rank's own tiles (1/N of the film) to rank 0" if name == "tiles" else "ncclReduce(sum) of the film to rank 0"}
         grp.set_camera(cam)
 
+    # ---- C4 / C5 of BASELINE.json (N > 1 only): the 52 M-triangle city at 4K by tiles, and a progressive 4K render with the film
+    # assembled at checkpoints — through the same group, so that the driver's scaling run exercises them
+    c4 = c5 = None
+    if grp is not None and not args.no_c4c5:
+        from vermilion_b200 import scenes as _scenes
+        try:
+            t0 = time.time()
+            root = rank == 0
+            cpos = cnrm = cuv = None
+            if root:
+                cpos, cnrm, cuv = _scenes.city(64, 64, 24, 2024)
+            gen_s = time.time() - t0
+            grp.set_scene(cpos, cnrm, cuv, broadcast=True)  # 5 GB up on rank 0's link, then NVLink
+            ntri = grp.member_stats(0)["n_triangles"]
+            del cpos, cnrm, cuv
+            c4w, c4h, c4spp = 3840, 2160, 256
+            mk = lambda spp: engine.camera_from_settings(c4w, c4h, (0.0, 900.0, 1950.0), (25.0, 0.0, 0.0), 6.0, (3.6, 3.6 * c4h / c4w), spp)
+            grp.set_camera(mk(4))
+            grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=engine.DIST_SPLIT_TILES)  # warm-up
+            grp.set_camera(mk(c4spp))
+            fn = lambda: grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=engine.DIST_SPLIT_TILES)
+            cms, csts = timed(fn, 1, 0)
+            crays = torch.tensor([float(csts[0]["rays_traced"]), csts[0]["total_ms"]], dtype=torch.float64, device=dev)
+            allr = [torch.zeros_like(crays) for _ in range(world)]
+            dist.all_gather(allr, crays)
+            tot_rays = sum(float(x[0]) for x in allr)
+            per_rank = [float(x[1]) for x in allr]
+            full = None
+            if root:
+                film = grp.read_image(engine.FILM_SUM)
+                full = bool((film[:, 3] == c4spp).all())
+                del film
+            c4 = {"workload": f"C4: city 64x64 blocks, {ntri} triangles, {c4w}x{c4h}, {c4spp} spp, FIXED, interleaved 64x64 tiles over {world} GPUs, tile gather to rank 0",
+                  "ms_per_frame": cms, "mrays_per_s": tot_rays / cms / 1e3, "spp_per_s": c4spp / (cms / 1e3), "render_ms_per_rank": per_rank,
+                  "slowest_rank_ms": max(per_rank), "wall_over_slowest_rank": cms / max(per_rank), "assembly_ms_root": grp.stats()["collective_ms"],
+                  "every_pixel_has_spp_samples": full, "scene_gen_s_rank0": gen_s, "bvh_build_ms": grp.member_stats(0)["build_ms"]}
+        except Exception as e:
+            c4 = {"error": repr(e)}
+        try:
+            grp.set_scene(pos, nrm, uv)  # back to C2
+            c5w, c5h, per_gpu, k = 3840, 2160, 512, 64
+            c5spp = per_gpu * world
+            grp.set_camera(engine.camera_from_settings(c5w, c5h, CAM_POS, CAM_ROT, 6.0, (3.6, 3.6 * c5h / c5w), c5spp))
+            checkpoints = [c for c in (64 * world, 256 * world, c5spp) if c <= c5spp]
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world > 1:
+                dist.barrier()
+            a.record(stream)
+            done, rays5, asm_ms, first = 0, 0, 0.0, True
+            for cp in checkpoints:
+                while done < cp:
+                    step_n = min(k * world, cp - done)
+                    last = done + step_n == cp
+                    grp.render(mode=engine.MODE_FIXED, seed=1, max_segments=5, split=engine.DIST_SPLIT_SAMPLES, sample_begin=done,
+                               sample_end=done + step_n, accumulate=not first, assemble=last)
+                    first = False
+                    done += step_n
+                    rays5 += grp.member_stats(0)["rays_traced"]
+                    if last:
+                        asm_ms += grp.stats()["collective_ms"]
+            b.record(stream); b.synchronize()
+            barrier()
+            t5 = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev); dist.all_reduce(t5, op=dist.ReduceOp.MAX)
+            r5 = torch.tensor([float(rays5)], dtype=torch.float64, device=dev); dist.all_reduce(r5, op=dist.ReduceOp.SUM)
+            ok = None
+            if rank == 0:
+                film = grp.read_image(engine.FILM_SUM)
+                ok = bool((film[:, 3] == c5spp).all() and np.isfinite(film).all())
+                del film
+            c5 = {"workload": f"C5: C2 scene, {c5w}x{c5h}, {c5spp} spp progressive ({per_gpu} per GPU; BASELINE's 4096 spp is the N = 8 case), passes of {k} spp per GPU, "
+                              f"sample slices over {world} GPUs, film assembled on rank 0 (ncclReduce) at {checkpoints} spp",
+                  "ms": float(t5[0]), "mrays_per_s": float(r5[0]) / float(t5[0]) / 1e3, "spp_per_s": c5spp / (float(t5[0]) / 1e3),
+                  "spp_per_s_1080p_equiv": c5spp * (c5w * c5h) / (1920 * 1080) / (float(t5[0]) / 1e3), "assembly_ms_root_total": asm_ms,
+                  "assemblies": len(checkpoints), "film_bytes": c5w * c5h * 16, "every_pixel_has_spp_samples": ok,
+                  "rmse": "converged-image RMSE against the compiled reference is asserted by tests/test_golden.py::test_gpu_converged_image_rmse (4096 spp); "
+                          "the 4K frame itself took the CPU reference 673 s for 8 rows (profiles/r01_c5_n8.json: 0.0280 vs floor 0.0281)"}
+        except Exception as e:
+            c5 = {"error": repr(e)}
+        grp.set_scene(pos, nrm, uv)
+        grp.set_camera(cam)
+
     # ---- e2e: host buffers through the C ABI, every step: scene upload + BVH build + render + image read-back ----
     ppos = torch.from_numpy(pos).pin_memory().numpy(); pnrm = torch.from_numpy(nrm).pin_memory().numpy(); puv = torch.from_numpy(uv).pin_memory().numpy()
     pimg = torch.empty((npix, 5), dtype=torch.float32).pin_memory().numpy()  # the caller's (pinned) image buffer, like Camera::mImage
@@ -416,7 +499,7 @@ def main():
                       "l2": "256 MiB L2 flush between timed steps", "paths_in_flight": args.max_paths},
            "spp_per_s": paths_all / npix / (ms / 1e3), "rays_per_step": rays_all / args.steps, "bvh_build_ms": build_ms,
            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_c3": roofline_c3, "strong": strong,
-           "cpu_baseline": cpu}
+           "c4": c4, "c5": c5, "cpu_baseline": cpu}
     if eng is not None:
         eng.close()
     if grp is not None:

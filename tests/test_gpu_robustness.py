@@ -19,42 +19,55 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TINY = os.path.join(ROOT, "vermilion_b200", "variants", "libvermilion_b200_tinystack.so")
 
 _CHILD = r"""
-import sys, numpy as np
+import sys, zlib, numpy as np
 sys.path[:0] = [%(root)r, %(root)r + "/tests"]
+import common
 from vermilion_b200 import engine, scenes
-pos, nrm, uv = scenes.spheres(2, 1, 3, 150.0)   # 2560 triangles: four or five wide levels
-rays = scenes.uniform_rays(20000, seed=7, lo=-400.0, hi=900.0)
+pos, nrm, uv = scenes.spheres(2, 1, 5, 150.0)   # 40 960 triangles: seven wide levels
+rays = common.aimed_rays(pos, 20000, 3)          # every ray walks down to a leaf
 e = engine.Engine(device=0)
 try:
     e.set_scene(pos, nrm, uv)
-    print("COMMIT_OK depth", e.stats()["wide_depth"])
+    print("COMMIT_OK depth", e.stats()["wide_depth"], flush=True)
 except engine.VmnError as x:
-    print("COMMIT_REFUSED", x)
+    print("COMMIT_REFUSED", x, flush=True)
     sys.exit(0)
 for flags in (0, engine.ISECT_BVH2):
     try:
-        e.intersect(rays, flags)
-        print("INTERSECT_OK", flags)
+        h = e.intersect(rays, flags)
+        print("INTERSECT_OK", flags, zlib.crc32(h.tobytes()), flush=True)
     except engine.VmnError as x:
-        print("INTERSECT_REPORTED", flags, x)
+        print("INTERSECT_REPORTED", flags, x, flush=True)
 """
 
 
-def _run_tiny(extra_env):
-    env = dict(os.environ, VMN_LIB=TINY, **extra_env)
-    r = subprocess.run([sys.executable, "-c", _CHILD % {"root": ROOT}], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+def _run_child(extra_env):
+    env = dict(os.environ, **extra_env)
+    r = subprocess.run([sys.executable, "-c", _CHILD % {"root": ROOT}], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180)
     return r.stdout
 
 
 def test_too_deep_tree_is_refused_at_commit_and_overflow_is_reported():
-    """the `tinystack` build of the library (3 stack entries; built by __graft_entry__.build()) makes an ordinary scene 'too deep'"""
+    """The `tinystack` build of the library (3 stack entries, built by __graft_entry__.build()) makes an ordinary scene 'too deep':
+    the commit is refused with VMN_ERR_STATE; with the depth check switched off (test hook) every traversal call either REPORTS the
+    overflow (VMN_ERR_STATE) or returns exactly what the normal library returns — never a silently wrong hit."""
     assert os.path.exists(TINY), "variants/libvermilion_b200_tinystack.so missing: run __graft_entry__.build()"
-    out = _run_tiny({})
+    out = _run_child({"VMN_LIB": TINY})
     assert "COMMIT_REFUSED" in out and "STATE" in out and "exceeds the traversal stack" in out, out
-    out = _run_tiny({"VMN_DEBUG_NO_DEPTH_CHECK": "1"})
+    good = _run_child({})
+    assert good.count("INTERSECT_OK") == 2, good
+    want = {l.split()[1]: l.split()[2] for l in good.splitlines() if l.startswith("INTERSECT_OK")}
+    out = _run_child({"VMN_LIB": TINY, "VMN_DEBUG_NO_DEPTH_CHECK": "1"})
     assert "COMMIT_OK" in out, out
-    # both traversals drop pushes on this tree with three entries; each call must say so (VMN_ERR_STATE), not return hits
-    assert out.count("INTERSECT_REPORTED") == 2 and "traversal stack overflowed" in out, out
+    lines = [l for l in out.splitlines() if l.startswith("INTERSECT_")]
+    assert len(lines) == 2, out
+    for l in lines:
+        f = l.split()
+        if f[0] == "INTERSECT_OK":
+            assert f[2] == want[f[1]], "a traversal with a 3-entry stack returned different hits WITHOUT reporting: " + out
+        else:
+            assert "traversal stack overflowed" in l, out
+    assert any(l.startswith("INTERSECT_REPORTED") for l in lines), out  # seven levels cannot fit three entries
 
 
 def test_checked_build_runs_every_kernel_without_a_bounds_violation():

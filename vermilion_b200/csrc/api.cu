@@ -92,23 +92,14 @@ static void apply_l2_policy(vmn_ctx* c) {
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
     cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
     cudaStreamAttrValue v{};
-    // mode 1: everything a ray walks, when it fits the carve-out; mode 2: the wide nodes alone (the upper tree is what every ray shares),
-    // with a hit ratio when they exceed the carve-out — the out-of-cache experiment (C3: 107 MB of nodes, 640 MB of triangles)
-    const uint64_t node_bytes = (uint64_t)c->n_wide * sizeof(vmn::WideNode);
-    const bool nodes_only = enabled == 2 && node_bytes > 0 && max_persist > 0;
-    const bool want = nodes_only || (enabled == 1 && c->trav_bytes > 0 && max_persist > 0 && c->trav_bytes <= (uint64_t)max_persist && c->trav_bytes <= (uint64_t)max_window);
+    // (a window over the wide nodes alone, with a hit ratio, for scenes that exceed the carve-out — C3: 107 MB of nodes — measured no
+    // gain either: 910.7 against 909.1 Mrays/s, profiles/r02c_ab_c3.txt; removed)
+    const bool want = enabled == 1 && c->trav_bytes > 0 && max_persist > 0 && c->trav_bytes <= (uint64_t)max_persist && c->trav_bytes <= (uint64_t)max_window;
     if (want) {
         cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist);
-        if (nodes_only) {
-            const uint64_t bytes = node_bytes < (uint64_t)max_window ? node_bytes : (uint64_t)max_window;
-            v.accessPolicyWindow.base_ptr = const_cast<vmn::WideNode*>(c->scene.nodes);
-            v.accessPolicyWindow.num_bytes = (size_t)bytes;
-            v.accessPolicyWindow.hitRatio = bytes <= (uint64_t)max_persist ? 1.0f : (float)((double)max_persist / (double)bytes);
-        } else {
         v.accessPolicyWindow.base_ptr = c->tris.p;
         v.accessPolicyWindow.num_bytes = (size_t)c->trav_bytes;
         v.accessPolicyWindow.hitRatio = 1.0f;
-        }
         v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
         v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
         c->l2_window = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess;
@@ -119,7 +110,7 @@ static void apply_l2_policy(vmn_ctx* c) {
         c->l2_window = false;
     }
     cudaGetLastError();
-    c->stats.l2_persist_bytes = c->l2_window ? (nodes_only ? node_bytes : c->trav_bytes) : 0;
+    c->stats.l2_persist_bytes = c->l2_window ? c->trav_bytes : 0;
 }
 
 

@@ -518,10 +518,6 @@ vmn_status build_bvh(vmn_ctx* c) {
 
     c->scene.nodes = wide_nodes;
     c->scene.n_wide = (uint32_t)c->n_wide;
-    // out-of-cache scenes (what a ray walks does not fit the 126 MB L2: C3, C4) get the latency-hiding prefetches of trav_node;
-    // env VMN_OOC=<bit mask> overrides (0 = none, 1 = leaf triangles, 2 = sibling nodes, 3 = both)
-    { const char* e = getenv("VMN_OOC");
-      c->scene.ooc = e ? (uint32_t)atoi(e) : ((sizeof(LeafTri) * (uint64_t)n + sizeof(WideNode) * (uint64_t)c->n_wide) > (96ull << 20) ? (VMN_OOC_PREFETCH_TRIS | VMN_OOC_PREFETCH_SIBS) : 0u); }
     c->trav_bytes = sizeof(LeafTri) * (uint64_t)n + sizeof(WideNode) * (uint64_t)c->n_wide;
     c->scene.tris = c->tris.as<LeafTri>();
     c->scene.tris_sorted = c->tris_sorted.as<TriRec>();

@@ -109,9 +109,6 @@ constexpr uint32_t kTravStackCap = VMN_STACK_CAP;
 #define VMN_CHECK(errp, cond) ((void)0)
 #endif
 
-#define VMN_OOC_PREFETCH_TRIS 1u // at a node visit, start fetching the first triangle of every hit leaf into the L2
-#define VMN_OOC_PREFETCH_SIBS 2u // ... and the hit internal children that are visited later (after the first one's subtree)
-
 struct SceneDev {
     uint32_t* err;           // device error word owned by the context (VMN_DEVERR_*), checked at every synchronising entry point
     const WideNode* nodes;   // BVH8
@@ -122,7 +119,6 @@ struct SceneDev {
     Bvh2 bvh2;
     uint32_t n_tris;
     uint32_t n_wide;         // wide nodes in use
-    uint32_t ooc;            // out-of-cache scene (nodes + leaf triangles exceed the L2): VMN_OOC_* latency-hiding measures of the traversal
     uint32_t n_spheres;
     const float* tex;        // texture slot 0 or nullptr
     uint32_t tex_w, tex_h, tex_c;

@@ -51,6 +51,18 @@ namespace vmn {
 
 static_assert(VMN_SH_STACK + VMN_LOCAL_STACK == (int)kTravStackCap, "shared + local stack entries must add up to kTravStackCap");
 
+#ifndef VMN_DEFER_STORE
+#define VMN_DEFER_STORE 1 // store a finished ray's result with the next refill (several idle lanes) instead of at once: C3 1302 -> 1407 Mrays/s,
+                          // C2 unchanged (profiles/r02d_ab_bisect.txt). Tried with it and dropped: prefetch.global.L2 of every hit leaf's first
+                          // triangle (C3 +-0) and of the hit sibling nodes that are visited later (C3 -10 %; both +2.3 % on C2's k_extend)
+#endif
+#ifndef VMN_ABANDON
+#define VMN_ABANDON 0     // stack overflow: 1 = abandon the ray after reporting, 0 = report and go on without the dropped siblings. The early
+                          // return of 1 costs the node loop its load scheduling: k_extend +39 % on C2, C3 1390 -> 1020 Mrays/s
+                          // (profiles/r02d_ab_bisect.txt). The branch is unreachable in the product build (commit refuses trees deeper than
+                          // the 128-entry stack); the 3-entry `tinystack` test build, where it is reached, is compiled with 1.
+#endif
+
 struct TravCounters { unsigned long long nodes, tris; };
 
 // Queue traffic (rays in, hits out, rays appended by the shading stage) is touched once per launch and is far larger than the L2: it is
@@ -206,8 +218,10 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
             else if (s.sp < VMN_SH_STACK + VMN_LOCAL_STACK) { lstack[s.sp - VMN_SH_STACK] = s.ng; ++s.sp; }
             else { // report, and abandon this ray: nothing pending, nothing stacked -> trav_pop ends it
                 atomicOr(sc.err, VMN_DEVERR_STACK);
+#if VMN_ABANDON
                 s.ng = make_uint2(0u, 0u); s.tg = make_uint2(0u, 0u); s.sp = 0;
                 return;
+#endif
             }
         }
         VMN_CHECK(sc.err, nidx < sc.n_wide && s.sp >= 0 && s.sp <= (int)kTravStackCap);
@@ -289,20 +303,6 @@ __device__ __forceinline__ void trav_node(Trav& s, const SceneDev& sc, uint2* ss
                 hl &= hl - 1u;
                 const uint32_t m = __byte_perm(q1.z, q1.w, j) & 0xFFu; // byte j of the 8 meta bytes
                 hitmask |= (m >> 5) << (m & 31u);
-                // out-of-cache scenes: the pooled triangle phase runs a few node steps from now; its DRAM round trip starts here
-                if (sc.ooc & VMN_OOC_PREFETCH_TRIS) asm volatile("prefetch.global.L2 [%0];" ::"l"(sc.tris + (q1.y + (m & 31u))));
-            }
-            if ((sc.ooc & VMN_OOC_PREFETCH_SIBS) && (x & (x - 1u))) {
-                // hit internal children other than the one visited next: they are popped after that child's whole subtree (tens of
-                // microseconds later, well inside the L2's residence time): fetch them into the L2 now
-                uint32_t rest = x & ~(1u << (31u - __clz(x)));
-                while (rest) {
-                    const uint32_t slot = (31u - __clz(rest)) ^ s.oct_inv;
-                    rest &= ~(1u << (31u - __clz(rest)));
-                    const uint4* sp4 = nodes + (uint64_t)kNodeStride16 * (q1.x + __popc(imask & ((1u << slot) - 1u)));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(sp4));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(sp4 + 4));
-                }
             }
         }
 #else
@@ -541,7 +541,11 @@ __device__ __forceinline__ void persistent_trace(const SceneDev& sc, uint64_t n,
         if (active) trav_tris<COUNT>(s, sc, cnt);
 #endif
         if (active && s.tg.y == 0u && !trav_pop(s, sstack, sstride, lstack)) {
+#if VMN_DEFER_STORE
             s.sp = -1;
+#else
+            store(ray, s);
+#endif
             active = false;
         }
     }

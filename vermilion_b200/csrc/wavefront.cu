@@ -617,7 +617,7 @@ vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* ou
     return VMN_OK;
 }
 
-static bool mega_wanted(uint64_t n_local);
+static bool mega_wanted(const vmn_ctx* c, uint64_t n_local);
 static vmn_status render_mega(vmn_ctx* c, const vmn_render_params* prm, const PixelMap& pm, uint64_t n_local);
 
 vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
@@ -638,7 +638,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     if ((prm->flags & VMN_RENDER_ACCUMULATE) && mode != VMN_MODE_FIXED) return fail(c, VMN_ERR_INVALID, "VMN_RENDER_ACCUMULATE needs VMN_MODE_FIXED");
     if (!(prm->flags & VMN_RENDER_ACCUMULATE)) VMN_CUDA(c, cudaMemsetAsync(c->film.p, 0, 16 * npix, c->stream));
     if (n_local_total == 0 || s_begin == s_end) return VMN_OK;
-    if (mode == VMN_MODE_COMPAT && mega_wanted(n_local_total)) {
+    if (mode == VMN_MODE_COMPAT && mega_wanted(c, n_local_total)) {
         if (spp / 4 == 0) return VMN_OK; // spp < 4: the reference takes no samples at all
         return render_mega(c, prm, pm, n_local_total);
     }
@@ -778,7 +778,7 @@ __device__ __forceinline__ void bf_camera_ray(const CamDev& c, uint64_t p, float
 }
 
 __global__ void __launch_bounds__(kWfBlock) k_bf_raygen(CamDev cam, PixelMap pm, BfParams bp, const uint2* __restrict__ meta, float4* __restrict__ rays,
-                                                        uint32_t* __restrict__ qcount) {
+                                                        uint32_t* __restrict__ qcount, unsigned long long* __restrict__ samples_started) {
     const uint64_t lp = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = lp < bp.n_local;
     uint64_t pixel = 0;
@@ -793,7 +793,7 @@ __global__ void __launch_bounds__(kWfBlock) k_bf_raygen(CamDev cam, PixelMap pm,
     if (ballot == 0u) return;
     const uint32_t lane = threadIdx.x & 31u;
     uint32_t base = 0;
-    if (lane == (uint32_t)(__ffs(ballot) - 1)) base = atomicAdd(qcount, (uint32_t)__popc(ballot));
+    if (lane == (uint32_t)(__ffs(ballot) - 1)) { base = atomicAdd(qcount, (uint32_t)__popc(ballot)); atomicAdd(samples_started, (unsigned long long)__popc(ballot)); }
     base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
     if (live) {
         const uint32_t q = base + __popc(ballot & ((1u << lane) - 1u));
@@ -1064,11 +1064,14 @@ __global__ void __launch_bounds__(kWfBlock) k_mega_bf(SceneDev sc, const SphereD
     atomicAdd(frame_ctr + 3, (unsigned long long)n);
 }
 
-// VMN_MEGA=0 never, 1 always, unset: frames of up to 4 Mi pixels (1080p is 2 Mi). Read at every render (tests switch it).
-static bool mega_wanted(uint64_t n_local) {
+// VMN_MEGA=0 never, 1 always, unset: frames of up to 4 Mi pixels over scenes of up to 64 Ki triangles. Measured (profiles/r02c_*): C1
+// (30 triangles, 512 x 512, COMPAT) 6.08 -> 1.40 ms end to end, 240 launches -> 1; but BruteForce at 1080p over C2's 983 040 triangles is
+// throughput-bound, not launch-bound — 2.35 ms as a wavefront (5.3 Grays/s through the pooled persistent traversal) against 3.74 ms as one
+// divergent per-thread kernel — so large scenes keep the wavefront. Read at every render (tests switch it).
+static bool mega_wanted(const vmn_ctx* c, uint64_t n_local) {
     const char* e = getenv("VMN_MEGA");
     if (e && *e) return atoi(e) != 0;
-    return n_local <= (4ull << 20);
+    return n_local <= (4ull << 20) && c->n_tris <= (64ull << 10);
 }
 
 static vmn_status render_mega(vmn_ctx* c, const vmn_render_params* prm, const PixelMap& pm, uint64_t n_local) {
@@ -1117,7 +1120,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
     VMN_CUDA(c, cudaMemsetAsync(c->film_aux.p, 0, 8 * npix, c->stream));
     c->film_bf = true;
     if (n_local_total == 0 || spp == 0) return VMN_OK; // spp == 0: the reference divides 0 by 0; here the film stays empty
-    if (mega_wanted(n_local_total)) return render_mega(c, prm, pm, n_local_total);
+    if (mega_wanted(c, n_local_total)) return render_mega(c, prm, pm, n_local_total);
 
     const uint32_t stride = (prm->flags & VMN_RENDER_BF_SHADOW) ? 2u : 1u;
     uint64_t chunk = c->max_paths / stride;
@@ -1146,14 +1149,17 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
             bp.sample = sample;
             VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 16, c->stream)); // queue counts + the two claim counters used below
             clk.begin(ST_RAYGEN);
-            k_bf_raygen<<<cdiv64(bp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, bp, p->meta.as<uint2>(), p->ray[0].as<float4>(), qc);
+            k_bf_raygen<<<cdiv64(bp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, bp, p->meta.as<uint2>(), p->ray[0].as<float4>(), qc,
+                                                                                  reinterpret_cast<unsigned long long*>(p->ctl.as<char>() + kOffFrame) + 3);
             clk.end();
             ++c->stats.kernel_launches;
-            VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
-            VMN_CUDA(c, cudaStreamSynchronize(c->stream));
-            const uint64_t live = p->h_count[0];
-            if (live == 0) break;
-            c->stats.paths_traced += live;
+            // The host only needs the live count to know when to stop launching: it is read after every fourth sample (a stage that
+            // finds its queue empty returns at once), the samples started are counted on the device (frame counter 3).
+            if ((sample & 3u) == 3u || sample + 1 == spp) {
+                VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
+                VMN_CUDA(c, cudaStreamSynchronize(c->stream));
+                if (p->h_count[0] == 0) break;
+            }
             if ((s = launch_extend(c, p, 0, 0, &clk, grid)) != VMN_OK) return s;
             clk.begin(ST_SHADE);
             k_bf_shade1<<<c->sm_count * 8, kWfBlock, 0, c->stream>>>(c->scene, sph, pm, bp, p->ray[0].as<float4>(), p->hit.as<float2>(), qc,
@@ -1180,9 +1186,9 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
     double st[4] = {0, 0, 0, 0};
     clk.collect(st);
     c->stats.raygen_ms = st[ST_RAYGEN]; c->stats.extend_ms = st[ST_EXTEND]; c->stats.shade_ms = st[ST_SHADE]; c->stats.resolve_ms = st[ST_RESOLVE];
-    unsigned long long h[3] = {0, 0, 0};
-    VMN_CUDA(c, cudaMemcpy(h, p->ctl.as<char>() + kOffFrame, 24, cudaMemcpyDeviceToHost));
-    c->stats.nodes_visited = h[0]; c->stats.tris_tested = h[1]; c->stats.rays_traced = h[2];
+    unsigned long long h[4] = {0, 0, 0, 0};
+    VMN_CUDA(c, cudaMemcpy(h, p->ctl.as<char>() + kOffFrame, 32, cudaMemcpyDeviceToHost));
+    c->stats.nodes_visited = h[0]; c->stats.tris_tested = h[1]; c->stats.rays_traced = h[2]; c->stats.paths_traced = h[3];
     return VMN_OK;
 }
 
