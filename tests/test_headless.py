@@ -90,3 +90,28 @@ def test_b200_engine_matches_the_cpu_engine_within_its_own_noise(tmp_path, pair)
     if cpu == "cpu":  # depth plane = samples taken; BruteForceTracer stores the last hit distance there instead
         assert abs(infos["gpu"]["mean_depth_plane"] - infos["cpu1"]["mean_depth_plane"]) <= 0.05 * infos["cpu1"]["mean_depth_plane"]
     assert infos["gpu"]["rays_traced"] > 160 * 120
+
+
+@pytest.mark.gpu
+@needs_headless
+@pytest.mark.parametrize("engine_name", ["b200", "b200-bf"])
+def test_headless_on_several_gpus_writes_the_same_png(tmp_path, engine_name):
+    """`--gpus N` / `--devices a,b,...`: the one Render call of the command line spread over several devices (B200Options::devices ->
+    vmn_dist local group, tiles). The PNG and the depth plane are byte-identical to the single-device run. On a one-GPU box the device list
+    repeats device 0 (peer-copy exchange); with two or more GPUs `--gpus 2` runs over NCCL as well."""
+    import torch
+    pos, nrm, uv = scenes.spheres(2, 2, 2, 150.0)
+    obj = scenes.write_obj(str(tmp_path / "spheres.obj"), pos, nrm, uv)
+    common = [obj, "--res", "200x136", "--spp", 32, "--camera", "0,500,1900,0,5,0", "--film", "6,3.6,2.448", "--quiet", "--engine", engine_name, "--seed", 5]
+    rc, one, err = run(common + ["--out", str(tmp_path / "one")])
+    assert rc == 0, err
+    variants = [("dup", ["--devices", "0,0,0"])]
+    if torch.cuda.device_count() >= 2:
+        variants.append(("nccl", ["--gpus", 2]))
+    for tag, extra in variants:
+        rc, info, err = run(common + extra + ["--out", str(tmp_path / tag)])
+        assert rc == 0, err
+        assert info["gpus"] == (3 if tag == "dup" else 2) and len(info["render_ms"]) == info["gpus"]
+        assert info["rays_traced"] == one["rays_traced"]
+        for suffix in (".png", "_depth.pfm"):
+            assert open(str(tmp_path / tag) + suffix, "rb").read() == open(str(tmp_path / "one") + suffix, "rb").read(), (tag, suffix)
