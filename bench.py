@@ -174,7 +174,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c4c5", action="store_true", help="skip the C4 / C5 records of an N > 1 run (52 M-triangle city at 4K; progressive 4K render)")
     ap.add_argument("--no-c3", action="store_true", help="skip the roofline_c3 record (10 M-triangle soup, N = 1 only)")
-    ap.add_argument("--max-paths", type=int, default=32 << 20, help="paths in flight (112 B each); larger batches amortise the tail of every persistent launch")
+    ap.add_argument("--max-paths", type=int, default=128 << 20, help="paths in flight (112 B each = 15 GB at the default: the whole 64-spp 1080p frame is ONE batch); larger batches amortise the tail of every persistent launch: 16 Mi 6826, 32 Mi 7063, 64 Mi 7172, 128 Mi 7221 Mrays/s (profiles/r02j_maxpaths.txt)")
     args = ap.parse_args()
     width, height = (int(x) for x in args.res.lower().split("x"))
     if args.impl == "reference":
