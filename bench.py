@@ -448,7 +448,9 @@ def main():
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             tr = json.load(f)["k_extend"]
         if tr.get("source_hash") == engine.kernel_source_hash():
-            traffic, traffic_note = tr["dram_bytes_per_launch"], tr.get("source", "")
+            # captured on launches of tr["rays_per_launch"] rays; scaled to the rays one launch of THIS run processes (per launch, like `achieved`)
+            traffic = tr["dram_bytes_per_launch"] / tr.get("rays_per_launch", 33177600) * (rays / max(1, n_extend))
+            traffic_note = tr.get("source", "") + f" Captured at {tr.get('rays_per_launch')} rays per launch = {tr['dram_bytes_per_launch'] / tr.get('rays_per_launch', 33177600):.1f} B per ray; scaled to this run's rays per launch."
         else:
             traffic_note = f"stale capture refused: taken on sources {tr.get('source_hash')}, this build is {engine.kernel_source_hash()}"
     except Exception as e:
