@@ -148,12 +148,15 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
 template <bool COUNT>
 __global__ void __launch_bounds__(kWfBlock, VMN_EXTEND_MINB) k_extend(SceneDev sc, const float4* __restrict__ rays, const uint32_t* __restrict__ qcount,
                                                      float2* __restrict__ hits, unsigned long long* next, TravCounters* gcnt,
-                                                     unsigned long long* total_rays, uint32_t refill_min) {
+                                                     unsigned long long* total_rays, uint32_t refill_min, uint32_t* __restrict__ qcount_other) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kWfBlock];
     __shared__ __align__(16) uint32_t wscratch_all[VMN_WSCRATCH * (kWfBlock / 32)];
     uint2* sstack = sstack_all + threadIdx.x;
     const uint64_t n = *qcount;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total_rays, (unsigned long long)n);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(total_rays, (unsigned long long)n);
+        *qcount_other = 0u; // the other queue is dead while this one is traced; the stage after this kernel appends to it from zero
+    }
     TravCounters cnt{0ull, 0ull};
     persistent_trace<COUNT>(sc, n, next, pick_chunk(n, gridDim.x * (kWfBlock / 32)), refill_min, sstack, kWfBlock, wscratch_all + VMN_WSCRATCH * (threadIdx.x >> 5), &cnt,
                             [&](uint64_t i, V3* o, V3* d) {
@@ -462,20 +465,38 @@ static CamDev cam_dev(const vmn_ctx* c) {
     return cd;
 }
 
-// per-stage device timing: event pairs around launches, summed after the stream drains
+// per-stage device timing, summed after the stream drains. Consecutive stages share ONE event (the end of a stage is the beginning of the
+// next): an event record is a stream operation of its own, and a frame is a chain of short launches — at two events per kernel plus a
+// 4-byte memset per bounce every launch carried about 21 us of stream overhead (profiles/r02j_maxpaths.txt). flush() closes the open stage
+// before work that belongs to no stage (memsets, copies) is enqueued.
 struct StageClock {
     vmn_ctx* c; PathPool* p;
-    std::vector<std::pair<size_t, int>> spans; // (index of start event, stage)
+    struct Span { size_t e0, e1; int stage; };
+    std::vector<Span> spans;
+    bool open = false;
     cudaEvent_t get() {
         if (p->ev_used == p->events.size()) { cudaEvent_t e; cudaEventCreate(&e); p->events.push_back(e); }
         return p->events[p->ev_used++];
     }
-    void begin(int stage) { spans.push_back({p->ev_used, stage}); cudaEventRecord(get(), c->stream); }
-    void end() { cudaEventRecord(get(), c->stream); }
+    void begin(int stage) {
+        const size_t e = p->ev_used;
+        cudaEventRecord(get(), c->stream);
+        if (open) spans.back().e1 = e;
+        spans.push_back({e, e, stage});
+        open = false;
+    }
+    void end() { open = true; } // closed by the next begin() or by flush()
+    void flush() {
+        if (!open) return;
+        spans.back().e1 = p->ev_used;
+        cudaEventRecord(get(), c->stream);
+        open = false;
+    }
     void collect(double ms[4]) {
+        flush();
         for (auto& s : spans) {
             float t = 0.f;
-            if (cudaEventElapsedTime(&t, p->events[s.first], p->events[s.first + 1]) == cudaSuccess) ms[s.second] += t;
+            if (s.e1 != s.e0 && cudaEventElapsedTime(&t, p->events[s.e0], p->events[s.e1]) == cudaSuccess) ms[s.stage] += t;
         }
     }
 };
@@ -509,9 +530,9 @@ static vmn_status launch_extend(vmn_ctx* c, PathPool* p, int cur, uint32_t it, S
     const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
     if (clk) clk->begin(ST_EXTEND);
     if (count)
-        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c));
+        k_extend<true><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c), qc + (cur ^ 1));
     else
-        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c));
+        k_extend<false><<<grid_extend, kWfBlock, 0, c->stream>>>(c->scene, p->ray[cur].as<float4>(), qc + cur, p->hit.as<float2>(), claims + it, gcnt, total, refill_min(c), qc + (cur ^ 1));
     if (clk) clk->end();
     ++c->stats.kernel_launches;
     return VMN_OK;
@@ -521,8 +542,7 @@ static vmn_status launch_extend(vmn_ctx* c, PathPool* p, int cur, uint32_t it, S
 static vmn_status bounce(vmn_ctx* c, PathPool* p, const PixelMap& pm, const RoundParams& rp, int cur, uint32_t it, int radiance_query,
                          StageClock* clk, int grid_extend) {
     uint32_t* qc = p->ctl.as<uint32_t>();
-    VMN_CUDA(c, cudaMemsetAsync(qc + (cur ^ 1), 0, 4, c->stream));
-    vmn_status s = launch_extend(c, p, cur, it, clk, grid_extend);
+    vmn_status s = launch_extend(c, p, cur, it, clk, grid_extend); // (k_extend also zeroes the count of the queue the shade stage appends to)
     if (s != VMN_OK) return s;
     if (clk) clk->begin(ST_SHADE);
     k_shade<<<c->sm_count * VMN_SHADE_MINB, kWfBlock, 0, c->stream>>>(c->scene, c->spheres.as<SphereDev>(), pm, rp, p->ray[cur].as<float4>(), p->hit.as<float2>(),
@@ -662,6 +682,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     const uint32_t max_seg = prm->max_segments ? prm->max_segments : 5;
     const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
     const int grid = extend_grid(c, count);
+    clk.flush();
     VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + kOffFrame, 0, 32, c->stream));
 
     VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
@@ -675,12 +696,14 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
             uint64_t live_px = rp.n_local;
             for (uint32_t round = 0; live_px; ++round) {
                 rp.s0 = round; rp.batch = 1;
+                clk.flush();
                 VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, p->cstate.as<uint32_t>(), p->ray[0].as<float4>(), qc,
                                                                                    p->radiance.as<float4>(), p->meta.as<uint32_t>());
                 clk.end();
                 ++c->stats.kernel_launches;
+                clk.flush();
                 VMN_CUDA(c, cudaMemcpyAsync(p->h_count + 2, qc, 4, cudaMemcpyDeviceToHost, c->stream)); // samples started; read after the next sync
                 int cur = 0;
                 uint64_t live = 1;
@@ -688,21 +711,24 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                     // four bounces per host round trip: the queue counts live on the device and a kernel that finds its queue empty returns
                     // at once, so the only thing the host needs is to know when to stop
                     for (int k = 0; k < 4; ++k, ++it) {
-                        if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
+                        if (it && it % kMaxClaims == 0) { clk.flush(); VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream)); }
                         if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
                         cur ^= 1;
                     }
+                    clk.flush();
                     VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + cur, 4, cudaMemcpyDeviceToHost, c->stream));
                     VMN_CUDA(c, cudaStreamSynchronize(c->stream));
                     live = p->h_count[0];
                 }
                 c->stats.paths_traced += p->h_count[2];
+                clk.flush();
                 VMN_CUDA(c, cudaMemsetAsync(qc + 4, 0, 4, c->stream));
                 clk.begin(ST_RESOLVE);
                 k_accumulate<<<cdiv64(rp.n_local, 256), 256, 0, c->stream>>>(pm, rp, spp, p->radiance.as<float4>(),
                                                                              c->film.as<float4>(), p->cstate.as<uint32_t>(), qc + 4);
                 clk.end();
                 ++c->stats.kernel_launches;
+                clk.flush();
                 VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc + 4, 4, cudaMemcpyDeviceToHost, c->stream));
                 VMN_CUDA(c, cudaStreamSynchronize(c->stream));
                 live_px = p->h_count[0];
@@ -710,6 +736,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
         } else {
             for (uint32_t s0 = s_begin; s0 < s_end; s0 += batch) {
                 rp.s0 = s0; rp.batch = (s_end - s0 < batch) ? s_end - s0 : batch;
+                clk.flush();
                 VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local * rp.batch, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, nullptr, p->ray[0].as<float4>(), qc,
@@ -720,7 +747,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 int cur = 0;
                 for (uint32_t it = 0; it < max_seg; ++it) {
                     // a claim counter serves one launch: recycle the block every kMaxClaims bounces (max_segments may exceed it)
-                    if (it && it % kMaxClaims == 0) VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream));
+                    if (it && it % kMaxClaims == 0) { clk.flush(); VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + 64, 0, 8 * kMaxClaims, c->stream)); }
                     if ((s = bounce(c, p, pm, rp, cur, it % kMaxClaims, 0, &clk, grid)) != VMN_OK) return s;
                     cur ^= 1;
                 }
@@ -1135,6 +1162,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
     const CamDev cd = cam_dev(c);
     const int grid = extend_grid(c, (c->flags & VMN_CFG_COUNTERS) != 0);
     const SphereDev* sph = c->spheres.as<SphereDev>();
+    clk.flush();
     VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + kOffFrame, 0, 32, c->stream));
 
     VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
@@ -1147,6 +1175,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
         VMN_CUDA(c, cudaMemsetAsync(p->meta.p, 0, 8 * bp.n_local, c->stream));      // (nTotalSamples, done)
         for (uint32_t sample = 0; sample < spp; ++sample) {
             bp.sample = sample;
+            clk.flush();
             VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 16, c->stream)); // queue counts + the two claim counters used below
             clk.begin(ST_RAYGEN);
             k_bf_raygen<<<cdiv64(bp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, bp, p->meta.as<uint2>(), p->ray[0].as<float4>(), qc,
@@ -1156,6 +1185,7 @@ vmn_status render_bruteforce(vmn_ctx* c, const vmn_render_params* prm) {
             // The host only needs the live count to know when to stop launching: it is read after every fourth sample (a stage that
             // finds its queue empty returns at once), the samples started are counted on the device (frame counter 3).
             if ((sample & 3u) == 3u || sample + 1 == spp) {
+                clk.flush();
                 VMN_CUDA(c, cudaMemcpyAsync(p->h_count, qc, 4, cudaMemcpyDeviceToHost, c->stream));
                 VMN_CUDA(c, cudaStreamSynchronize(c->stream));
                 if (p->h_count[0] == 0) break;
