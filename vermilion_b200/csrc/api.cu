@@ -212,8 +212,21 @@ vmn_status vmn_scene_set_spheres(vmn_ctx* c, const vmn_sphere* sp, uint32_t n) {
     CHECK_CTX(c);
     if (n > 16 || (n && !sp)) return fail(c, VMN_ERR_INVALID, "at most 16 spheres");
     SET_DEVICE(c);
-    static_assert(sizeof(vmn_sphere) == sizeof(SphereDev), "sphere layouts must match");
-    vmn_status s = upload(c, c->spheres, sp, sizeof(vmn_sphere) * (size_t)n);
+    SphereDev dev[16];
+    memset(dev, 0, sizeof(dev));
+    for (uint32_t i = 0; i < n; ++i) {
+        const vmn_sphere& a = sp[i];
+        SphereDev& d = dev[i];
+        d.cx = a.center[0]; d.cy = a.center[1]; d.cz = a.center[2];
+        const bool emitter = a.emission[0] != 0.f || a.emission[1] != 0.f || a.emission[2] != 0.f;
+        d.flags = (a.flags & VMN_SPH_FLIP_NORMAL) | (emitter ? VMN_SPHD_EMITTER : 0u);
+        const volatile float r2f = a.radius * a.radius; // one float rounding, as `rad * rad` in sphereIntersect (meshEngine.cpp:187)
+        d.r2 = (double)r2f;
+        d.r = a.radius;
+        d.ex = a.emission[0]; d.ey = a.emission[1]; d.ez = a.emission[2];
+        d.nx = a.normal_center[0]; d.ny = a.normal_center[1]; d.nz = a.normal_center[2];
+    }
+    vmn_status s = upload(c, c->spheres, dev, sizeof(SphereDev) * (size_t)n);
     if (s != VMN_OK) return s;
     VMN_CUDA(c, cudaStreamSynchronize(c->stream));
     c->n_spheres = n;

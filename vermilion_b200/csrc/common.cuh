@@ -126,7 +126,11 @@ struct SceneDev {
     uint32_t tex1_w, tex1_h, tex1_c;
 };
 
-struct __align__(16) SphereDev { float cx, cy, cz, r; float ex, ey, ez; uint32_t flags; float nx, ny, nz, pad; };
+// Device record of one analytic sphere, 64 B, laid out for the loop of raycast_finish: the first two 16-byte words are all a solve needs
+// (centre, flags with VMN_SPHD_EMITTER, and (double)(float)(r * r) — the reference's `(double)(rad * rad)` computed once on the host with
+// the same float multiply); emission and the point normals are measured from are only read for an accepted sphere.
+#define VMN_SPHD_EMITTER 0x100u // emission != (0,0,0): what meshEngine.cpp's accepted emitter blocks test implicitly by assigning Le
+struct __align__(16) SphereDev { float cx, cy, cz; uint32_t flags; double r2; float r, pad0; float ex, ey, ez, pad1; float nx, ny, nz, pad2; };
 
 // which pixels this context renders: a contiguous range or interleaved square tiles
 struct PixelMap {

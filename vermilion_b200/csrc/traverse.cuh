@@ -626,13 +626,13 @@ __device__ __forceinline__ void tri_bary(const TriRec& T, V3 hp, float* w1, floa
     *w2 = (d00 * d21 - d01 * d20) / denom;
 }
 
-// sphereIntersect (meshEngine.cpp:182-194): fp32 operands, fp64 solve, eps 1e-4.
-__device__ __forceinline__ float sphere_intersect(V3 pos, V3 rot, V3 p, const float rad) {
+// sphereIntersect (meshEngine.cpp:182-194): fp32 operands, fp64 solve, eps 1e-4. r2 = (double)(rad * rad), precomputed (SphereDev).
+__device__ __forceinline__ float sphere_intersect(V3 pos, V3 rot, V3 p, const double r2) {
     V3 op = p - pos;
     double t;
     const double eps = 1e-4;
     double b = (double)dot(op, rot);
-    double det = b * b - (double)dot(op, op) + (double)(rad * rad);
+    double det = b * b - (double)dot(op, op) + r2;
     if (det < 0) return 0;
     det = sqrt(det);
     return (float)((t = b - det) > eps ? t : ((t = b + det) > eps ? t : 0));
@@ -659,11 +659,12 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
     // after the loop, with the same expression (an IEEE normalize per accept was 11 % of k_shade).
     int last = -1;
     for (uint32_t i = 0; i < sc.n_spheres; ++i) {
-        const SphereDev s = sph[i];
-        const float th = sphere_intersect(o, d, V3(s.cx, s.cy, s.cz), s.r);
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(sph + i));      // centre, flags
+        const double2 s1 = __ldg(reinterpret_cast<const double2*>(sph + i) + 1); // r2, (r, pad)
+        const float th = sphere_intersect(o, d, V3(s0.x, s0.y, s0.z), s1.x);
         if (th > 0.f && th < nearest) {
             nearest = th;
-            if (s.ex != 0.f || s.ey != 0.f || s.ez != 0.f) r.Le = V3(s.ex, s.ey, s.ez);
+            if (__float_as_uint(s0.w) & VMN_SPHD_EMITTER) { const float4 e = __ldg(reinterpret_cast<const float4*>(sph + i) + 2); r.Le = V3(e.x, e.y, e.z); }
             last = (int)i;
         }
     }
