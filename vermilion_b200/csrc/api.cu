@@ -210,9 +210,9 @@ vmn_status vmn_scene_set_triangles(vmn_ctx* c, const float* pos, const float* nr
 
 vmn_status vmn_scene_set_spheres(vmn_ctx* c, const vmn_sphere* sp, uint32_t n) {
     CHECK_CTX(c);
-    if (n > 16 || (n && !sp)) return fail(c, VMN_ERR_INVALID, "at most 16 spheres");
+    if (n > kMaxSpheres || (n && !sp)) return fail(c, VMN_ERR_INVALID, "at most 16 spheres");
     SET_DEVICE(c);
-    SphereDev dev[16];
+    SphereDev dev[kMaxSpheres];
     memset(dev, 0, sizeof(dev));
     for (uint32_t i = 0; i < n; ++i) {
         const vmn_sphere& a = sp[i];

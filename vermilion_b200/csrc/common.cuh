@@ -109,6 +109,8 @@ constexpr uint32_t kTravStackCap = VMN_STACK_CAP;
 #define VMN_CHECK(errp, cond) ((void)0)
 #endif
 
+constexpr uint32_t kMaxSpheres = 16; // vmn_scene_set_spheres refuses more
+
 struct SceneDev {
     uint32_t* err;           // device error word owned by the context (VMN_DEVERR_*), checked at every synchronising entry point
     const WideNode* nodes;   // BVH8

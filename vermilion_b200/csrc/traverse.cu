@@ -29,8 +29,12 @@ __device__ __forceinline__ void load_ray(const vmn_ray* __restrict__ rays, uint6
     *o = V3(a.x, a.y, a.z); *d = V3(b.x, b.y, b.z);
 }
 
-template <bool WIDE, bool COUNT>
-__global__ void __launch_bounds__(kTraceBlock, VMN_TRACE_MINB) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
+#ifndef VMN_TRACE_MINB_OOC
+#define VMN_TRACE_MINB_OOC 9 // 56 registers for scenes the L2 cannot hold: latency-bound, one more CTA per SM is +2 % on C3 (r02u); 10 spills (-7 %)
+#endif
+
+template <bool WIDE, bool COUNT, int MINB = VMN_TRACE_MINB>
+__global__ void __launch_bounds__(kTraceBlock, MINB) k_intersect(SceneDev sc, const vmn_ray* __restrict__ rays, uint64_t n,
                                                            vmn_hit* __restrict__ out, unsigned long long* next, TravCounters* gcnt,
                                                            uint32_t refill_min) {
     __shared__ uint2 sstack_all[VMN_SH_STACK * kTraceBlock];
@@ -130,7 +134,12 @@ vmn_status launch_intersect(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_h
         VMN_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
 #define LAUNCH(W, C)                                                                                                           \
     k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt, refill_min(c))
-        if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
+        // out-of-cache scenes (same threshold as refill_min) run the 9-CTA build of the plain wide kernel; VMN_OOC_OCC=0 turns that off
+        static const bool ooc_occ = [] { const char* e = getenv("VMN_OOC_OCC"); return !(e && e[0] == '0'); }();
+        if (wide && !count && ooc_occ && c->trav_bytes > (96ull << 20))
+            k_intersect<true, false, VMN_TRACE_MINB_OOC><<<resident_grid(c, k_intersect<true, false, VMN_TRACE_MINB_OOC>), kTraceBlock, 0, c->stream>>>(
+                c->scene, d_rays, n, d_out, next, gcnt, refill_min(c));
+        else if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
         else { if (count) LAUNCH(false, true); else LAUNCH(false, false); }
 #undef LAUNCH
         VMN_CUDA(c, cudaGetLastError());

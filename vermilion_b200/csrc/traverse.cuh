@@ -649,7 +649,9 @@ struct RayCastOut {
 // Everything MeshEngine::RayCast does after the BVH query (meshEngine.cpp:364-508).
 // bvh_t / tri_id: closest BVH hit (original triangle id or VMN_MISS).
 __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const SphereDev* __restrict__ sph, V3 o, V3 d, float bvh_t,
-                                                     uint32_t tri_id) {
+                                                     uint32_t tri_id, const bool attrs = true) {
+    // attrs = false: the caller ends the path at this hit whatever it is (last segment of a FIXED path) and only reads hit / Le / dist —
+    // the triangle's two record gathers, the barycentrics and the normalisation are skipped
     RayCastOut r;
     r.N = V3(0, 0, 0); r.Le = V3(0, 0, 0); r.uv0 = 0.f; r.uv1 = 0.f; r.tri = tri_id;
     r.material = tri_id != VMN_MISS;
@@ -662,13 +664,14 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
         const float4 s0 = __ldg(reinterpret_cast<const float4*>(sph + i));      // centre, flags
         const double2 s1 = __ldg(reinterpret_cast<const double2*>(sph + i) + 1); // r2, (r, pad)
         const float th = sphere_intersect(o, d, V3(s0.x, s0.y, s0.z), s1.x);
+        const uint32_t sflags = __float_as_uint(s0.w);
         if (th > 0.f && th < nearest) {
             nearest = th;
-            if (__float_as_uint(s0.w) & VMN_SPHD_EMITTER) { const float4 e = __ldg(reinterpret_cast<const float4*>(sph + i) + 2); r.Le = V3(e.x, e.y, e.z); }
+            if (sflags & VMN_SPHD_EMITTER) { const float4 e = __ldg(reinterpret_cast<const float4*>(sph + i) + 2); r.Le = V3(e.x, e.y, e.z); }
             last = (int)i;
         }
     }
-    if (r.material) {
+    if (r.material && attrs) {
         V3 hp = o + d * bvh_t; // bvh.cpp:140
         VMN_CHECK(sc.err, tri_id < sc.n_tris);
         const TriRec T = load_tri(sc.tris_orig + tri_id);
@@ -684,7 +687,7 @@ __device__ __forceinline__ RayCastOut raycast_finish(const SceneDev& sc, const S
             r.N = normalize(-n);                    // triangle.cpp:86, meshEngine.cpp:369
         }
     }
-    if (last >= 0) {
+    if (last >= 0 && attrs) {
         const SphereDev s = sph[last];
         V3 nn = normalize(o + (d * nearest) - V3(s.nx, s.ny, s.nz));
         r.N = (s.flags & VMN_SPH_FLIP_NORMAL) ? -nn : nn;

@@ -276,11 +276,13 @@ __global__ void __launch_bounds__(kWfBlock, VMN_SHADE_MINB) k_shade(SceneDev sc,
             slot = __float_as_uint(ra.w);
             VMN_CHECK(sc.err, (uint64_t)slot < rp.n_local * (rp.batch ? rp.batch : 1u));
             V3 rStart(ra.x, ra.y, ra.z), rDir(rb.x, rb.y, rb.z);
-            const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y));
+            const uint32_t mt = __float_as_uint(rb.w); // path meta rides in the ray record: no dependent gather, no scatter per bounce
+            // the last segment of a FIXED path (every ray of that launch) ends here: no normal, uv or position wanted
+            const bool last_seg = rp.mode == VMN_MODE_FIXED && (mt >> 16) + 1u >= rp.max_segments;
+            const RayCastOut h = raycast_finish(sc, sph, rStart, rDir, hr.x, __float_as_uint(hr.y), !last_seg);
             // Path state traffic: the throughput stays exactly (1,1,1,1) until a textured diffuse bounce scales it, and the radiance only
             // changes on an emitter hit or at the first hit — so thr[] is not touched while kThrWritten is clear, and radiance[] is only
             // read-modified-written when the sum can change (x + 1*0 = x; with a written throughput it may be non-finite, so always then).
-            const uint32_t mt = __float_as_uint(rb.w); // path meta rides in the ray record: no dependent gather, no scatter per bounce
             uint32_t depth = mt & 0x7FFFu, segs = mt >> 16;
             const bool thr_written = (mt & kThrWritten) != 0u;
             float4 tp = thr_written ? thr[slot] : make_float4(1.f, 1.f, 1.f, 1.f);
