@@ -389,10 +389,15 @@ def main():
     ppos = torch.from_numpy(pos).pin_memory().numpy(); pnrm = torch.from_numpy(nrm).pin_memory().numpy(); puv = torch.from_numpy(uv).pin_memory().numpy()
     pimg = torch.empty((npix, 5), dtype=torch.float32).pin_memory().numpy()  # the caller's (pinned) image buffer, like Camera::mImage
     e2e_steps = max(1, min(args.steps, 3))
-    barrier()
-    t0 = time.perf_counter()
+    e2e_warm = 1 if args.warmup > 0 else 0  # one untimed pass of the same loop body: first-use allocations (staging, read-back) are not a step
     e2e_rays = 0
-    for _ in range(e2e_steps):
+    e2e_marks = [time.perf_counter()]  # host clock after every pass (this rank), the warm-up one included: reported as step_ms
+    for it in range(e2e_warm + e2e_steps):
+        if it == e2e_warm:
+            barrier()
+            t0 = time.perf_counter()
+            e2e_rays = 0
+            e2e_marks = [t0]
         if grp is not None:
             # the scene goes up once, on rank 0's PCIe link, and crosses NVLink to the other ranks; only rank 0 reads the image back
             root = rank == 0
@@ -406,6 +411,7 @@ def main():
             eng.render(mode=engine.MODE_FIXED, seed=1, max_segments=5)
             eng.read_image(out=pimg)
         e2e_rays += step_stats()["rays_traced"]
+        e2e_marks.append(time.perf_counter())
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
@@ -414,7 +420,8 @@ def main():
         b = te.clone(); dist.all_reduce(b, op=dist.ReduceOp.SUM)
         e2e_s, e2e_rays = float(a[0]), float(b[1])
     e2e = {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(pos.nbytes + nrm.nbytes + uv.nbytes + 8 * 64 + 48),
-           "d2h_bytes_per_step": int(pimg.nbytes), "steps": e2e_steps,
+           "d2h_bytes_per_step": int(pimg.nbytes), "steps": e2e_steps, "warmup": e2e_warm,
+           "step_ms": [round((y - x) * 1e3, 3) for x, y in zip(e2e_marks, e2e_marks[1:])],
            "includes": "vmn_scene_set_triangles (H2D from pinned host) + vmn_scene_commit (GPU BVH build) + vmn_render + vmn_read_image (D2H)" if grp is None else
                        "vmn_dist_scene_set_triangles (H2D on rank 0 + ncclBroadcast) + vmn_dist_scene_commit (every GPU builds its BVH) + vmn_dist_render "
                        "(64 spp per rank + ncclReduce to rank 0) + vmn_dist_read_image (D2H on rank 0 only)"}
