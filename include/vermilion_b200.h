@@ -126,7 +126,7 @@ typedef struct {
 typedef struct {
     uint64_t n_triangles, n_nodes, n_wide_nodes;
     uint64_t node_bytes, tri_bytes;   /* bytes of one node / triangle record as laid out in HBM */
-    double build_ms;                  /* last vmn_scene_commit, device time */
+    double build_ms;                  /* last BVH build (vmn_scene_set_triangles + vmn_scene_commit), device time */
     uint64_t rays_traced;             /* extend-stage rays of the last render / intersect call */
     uint64_t paths_traced;            /* samples finished by the last render */
     uint64_t nodes_visited, tris_tested; /* only with VMN_CFG_COUNTERS */
@@ -146,7 +146,9 @@ vmn_status vmn_set_stream(vmn_ctx* ctx, void* cuda_stream);
 vmn_status vmn_synchronize(vmn_ctx* ctx);
 
 /* scene (replaces MeshEngine::createBVH, meshEngine.cpp:649-724, and `new BVH(tris)`, bvh.cpp:155-279).
- * pos: 9 floats per triangle; nrm: 9 per triangle or NULL (zeros); uv: 6 per triangle or NULL. */
+ * pos: 9 floats per triangle; nrm: 9 per triangle or NULL (zeros); uv: 6 per triangle or NULL.
+ * The arrays are borrowed for the call only. The call already builds the position-only part of the BVH while the normals and uvs are
+ * still in flight (pinned host arrays: the two overlap); vmn_scene_commit finishes the build and reports its errors. */
 vmn_status vmn_scene_set_triangles(vmn_ctx* ctx, const float* pos, const float* nrm, const float* uv, uint64_t n);
 vmn_status vmn_scene_set_spheres(vmn_ctx* ctx, const vmn_sphere* spheres, uint32_t n); /* n <= 16; 0 disables */
 void vmn_reference_spheres(vmn_sphere out[8]); /* the eight spheres of meshEngine.cpp:377-500 */
@@ -154,7 +156,7 @@ void vmn_reference_spheres(vmn_sphere out[8]); /* the eight spheres of meshEngin
  * Radiance samples (pathtracer.cpp:62-80) and BruteForceTracer's normal map (integrators.cpp:98-106); slot 1 is BruteForceTracer's
  * albedo (integrators.cpp:141-147). data = NULL unbinds the slot. */
 vmn_status vmn_scene_set_texture(vmn_ctx* ctx, uint32_t slot, const float* data, uint32_t w, uint32_t h, uint32_t c);
-vmn_status vmn_scene_commit(vmn_ctx* ctx); /* builds the BVH on the GPU */
+vmn_status vmn_scene_commit(vmn_ctx* ctx); /* finishes the GPU BVH build (all of it when the triangles did not come through this context's own upload) */
 
 /* ray queries */
 #define VMN_ISECT_BVH2 1u /* traverse the binary LBVH instead of the compressed BVH8 (baseline / cross-check) */

@@ -159,6 +159,7 @@ void vmn_destroy(vmn_ctx* c) {
         dev_free(*b);
     for (DevBuf& b : c->build_scratch) dev_free(b);
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -197,14 +198,29 @@ vmn_status vmn_scene_set_triangles(vmn_ctx* c, const float* pos, const float* nr
     if (n && !pos) return fail(c, VMN_ERR_INVALID, "pos is NULL");
     SET_DEVICE(c);
     c->committed = false;
+    c->geometry_built = false;
     c->n_tris = 0;
     vmn_status s;
     if ((s = upload(c, c->pos, pos, 36ull * n)) != VMN_OK) return s;
     c->have_nrm = nrm != nullptr; c->have_uv = uv != nullptr;
-    if (nrm && (s = upload(c, c->nrm, nrm, 36ull * n)) != VMN_OK) return s;
-    if (uv && (s = upload(c, c->uv, uv, 24ull * n)) != VMN_OK) return s;
-    VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // host pointers are borrowed for the call only
+    // The normals and uvs (60 of the 96 bytes per triangle) follow the positions on a second stream while the main stream already builds
+    // the BVH from the positions (with pinned host arrays the two overlap: -1 ms per C2 scene load; pageable arrays are staged by the
+    // driver and simply serialise as before). The event keeps the two uploads from sharing the link, which would only delay the build.
+    if (nrm || uv) {
+        if (!c->copy_stream) VMN_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        if (nrm && (s = dev_reserve(c, c->nrm, 36ull * n)) != VMN_OK) return s;
+        if (uv && (s = dev_reserve(c, c->uv, 24ull * n)) != VMN_OK) return s;
+        VMN_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
+        VMN_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev[6], 0));
+        if (nrm && n) VMN_CUDA(c, cudaMemcpyAsync(c->nrm.p, nrm, 36ull * n, cudaMemcpyHostToDevice, c->copy_stream));
+        if (uv && n) VMN_CUDA(c, cudaMemcpyAsync(c->uv.p, uv, 24ull * n, cudaMemcpyHostToDevice, c->copy_stream));
+    }
     c->n_tris = n;
+    c->geometry_status = build_geometry(c); // synchronises the main stream; a failure is reported by vmn_scene_commit
+    c->geometry_err = c->geometry_status == VMN_OK ? std::string() : c->err;
+    c->geometry_built = true;
+    if (c->copy_stream) VMN_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // host pointers are borrowed for the call only
     return VMN_OK;
 }
 
@@ -284,7 +300,14 @@ vmn_status vmn_scene_set_texture(vmn_ctx* c, uint32_t slot, const float* data, u
 vmn_status vmn_scene_commit(vmn_ctx* c) {
     CHECK_CTX(c);
     SET_DEVICE(c);
-    vmn_status s = build_bvh(c);
+    vmn_status s;
+    if (c->geometry_built) { // vmn_scene_set_triangles built it beside the upload
+        c->geometry_built = false;
+        if (c->geometry_status != VMN_OK) return fail(c, c->geometry_status, "%s", c->geometry_err.c_str());
+        s = build_records(c);
+    } else {
+        s = build_bvh(c);
+    }
     if (s != VMN_OK) return s;
     apply_l2_policy(c);
     c->scene.n_spheres = c->n_spheres;

@@ -409,7 +409,10 @@ __global__ void k_collapse(const uint2* __restrict__ q_in, uint32_t n_in, uint2*
 
 static inline uint32_t cdiv(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
 
-vmn_status build_bvh(vmn_ctx* c) {
+// The build in two parts. build_geometry needs the positions only (bounds, Morton order, hierarchy, cost table, collapse): it is what
+// vmn_scene_set_triangles runs while the normals and uvs are still crossing PCIe on the copy stream. build_records turns positions +
+// normals + uvs into the by-original-id records k_shade gathers; vmn_scene_commit runs it once everything has arrived.
+vmn_status build_geometry(vmn_ctx* c) {
     const uint64_t n64 = c->n_tris;
     if (n64 >= 0x7FFFFFF0ull) return fail(c, VMN_ERR_INVALID, "too many triangles (%llu)", (unsigned long long)n64);
     const uint32_t n = (uint32_t)n64;
@@ -471,7 +474,6 @@ vmn_status build_bvh(vmn_ctx* c) {
                                             vals2.as<uint32_t>(), (int)n, 0, 63, st));
     k_leaves<<<cdiv(n, B), B, 0, st>>>(pos, vals2.as<uint32_t>(), n, pmin.as<float4>(), pmax.as<float4>(), c->b_min.as<float4>(),
                                        c->b_max.as<float4>(), c->tris_sorted.as<TriRec>(), count.as<uint32_t>());
-    k_orig_records<<<cdiv(n, B), B, 0, st>>>(pos, c->have_nrm ? c->nrm.as<float>() : nullptr, c->have_uv ? c->uv.as<float>() : nullptr, n, c->tris_orig.as<TriRec>(), c->shade.as<ShadeRec>());
     TRYCUDA(cudaMemsetAsync(flags.p, 0, 4ull * n, st));
     if (n > 1) {
         k_hierarchy<<<cdiv(n - 1, B), B, 0, st>>>(keys2.as<uint64_t>(), (int)n, c->b_child.as<int2>(), parent.as<int>(), first.as<int>());
@@ -531,6 +533,27 @@ vmn_status build_bvh(vmn_ctx* c) {
     c->stats.n_wide_nodes = c->n_wide;
     c->stats.build_ms = ms;
     return VMN_OK;
+}
+
+vmn_status build_records(vmn_ctx* c) {
+    const uint32_t n = (uint32_t)c->n_tris;
+    if (n == 0) return VMN_OK;
+    cudaStream_t st = c->stream;
+    VMN_CUDA(c, cudaEventRecord(c->ev[0], st));
+    k_orig_records<<<cdiv(n, 256), 256, 0, st>>>(c->pos.as<float>(), c->have_nrm ? c->nrm.as<float>() : nullptr, c->have_uv ? c->uv.as<float>() : nullptr, n,
+                                                 c->tris_orig.as<TriRec>(), c->shade.as<ShadeRec>());
+    VMN_CUDA(c, cudaGetLastError());
+    VMN_CUDA(c, cudaEventRecord(c->ev[1], st));
+    VMN_CUDA(c, cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
+    c->stats.build_ms += ms;
+    return VMN_OK;
+}
+
+vmn_status build_bvh(vmn_ctx* c) {
+    const vmn_status s = build_geometry(c);
+    return s != VMN_OK ? s : build_records(c);
 }
 
 } // namespace vmn

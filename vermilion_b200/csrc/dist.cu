@@ -398,7 +398,7 @@ vmn_status vmn_dist_scene_set_triangles(vmn_dist* g, const float* pos, const flo
     for (auto& mb : g->m) { // staging buffers everywhere; host arrays go up on the root only
         DCUDA(g, cudaSetDevice(mb.device));
         vmn_ctx* c = mb.ctx;
-        c->committed = false; c->n_tris = 0;
+        c->committed = false; c->geometry_built = false; c->n_tris = 0;
         vmn_status s;
         if ((s = dev_reserve(c, c->pos, 36ull * nn)) != VMN_OK || (have_nrm && (s = dev_reserve(c, c->nrm, 36ull * nn)) != VMN_OK) ||
             (have_uv && (s = dev_reserve(c, c->uv, 24ull * nn)) != VMN_OK))

@@ -34,6 +34,12 @@ struct vmn_ctx {
     uint64_t n_tris = 0;
     bool have_nrm = false, have_uv = false;
     bool committed = false;
+    // vmn_scene_set_triangles has already run build_geometry on these triangles (its status and message are kept for vmn_scene_commit,
+    // which reports a failed build exactly as it did when it ran the whole build itself)
+    bool geometry_built = false;
+    vmn_status geometry_status = VMN_OK;
+    std::string geometry_err;
+    cudaStream_t copy_stream = nullptr; // normals / uvs upload, behind the positions, beside the geometry build
 
     // built scene
     vmn::DevBuf tris, tris_sorted, tris_orig, shade, b_min, b_max, b_child; // tris: leaf triangles + wide nodes (one allocation)
@@ -82,7 +88,9 @@ vmn_status check_device_error(vmn_ctx* c); // synchronises the stream; VMN_ERR_S
     } while (0)
 
 // bvh_build.cu
-vmn_status build_bvh(vmn_ctx* c);
+vmn_status build_bvh(vmn_ctx* c);      // = build_geometry + build_records
+vmn_status build_geometry(vmn_ctx* c); // positions only
+vmn_status build_records(vmn_ctx* c);  // + normals, uvs
 
 // traverse.cu
 uint32_t refill_min(const vmn_ctx* c); // idle lanes that trigger a refill in the persistent kernels (by scene size; env VMN_REFILL overrides)
