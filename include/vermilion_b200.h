@@ -237,7 +237,7 @@ enum { VMN_DIST_SPLIT_SAMPLES = 0, VMN_DIST_SPLIT_TILES = 1 };
 typedef struct {
     uint32_t world, local;                     /* ranks in the group / members in this process */
     double render_ms[VMN_DIST_MAX_RANKS];      /* device time of the last vmn_render of each LOCAL member */
-    double frame_ms, collective_ms, scene_ms;  /* root's stream: render + assembly, assembly alone; last broadcast scene upload */
+    double frame_ms, collective_ms, scene_ms;  /* root's stream: render + assembly, assembly alone; last broadcast scene load (upload, broadcast and the geometry build beside them) */
     uint64_t rays_traced;                      /* sum over the local members */
 } vmn_dist_stats;
 

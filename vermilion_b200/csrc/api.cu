@@ -206,19 +206,24 @@ vmn_status vmn_scene_set_triangles(vmn_ctx* c, const float* pos, const float* nr
     // The normals and uvs (60 of the 96 bytes per triangle) follow the positions on a second stream while the main stream already builds
     // the BVH from the positions (with pinned host arrays the two overlap: -1 ms per C2 scene load; pageable arrays are staged by the
     // driver and simply serialise as before). The event keeps the two uploads from sharing the link, which would only delay the build.
-    if (nrm || uv) {
+    const bool overlap = load_overlap();
+    cudaStream_t attr_stream = c->stream;
+    if ((nrm || uv) && overlap) {
         if (!c->copy_stream) VMN_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-        if (nrm && (s = dev_reserve(c, c->nrm, 36ull * n)) != VMN_OK) return s;
-        if (uv && (s = dev_reserve(c, c->uv, 24ull * n)) != VMN_OK) return s;
         VMN_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
         VMN_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev[6], 0));
-        if (nrm && n) VMN_CUDA(c, cudaMemcpyAsync(c->nrm.p, nrm, 36ull * n, cudaMemcpyHostToDevice, c->copy_stream));
-        if (uv && n) VMN_CUDA(c, cudaMemcpyAsync(c->uv.p, uv, 24ull * n, cudaMemcpyHostToDevice, c->copy_stream));
+        attr_stream = c->copy_stream;
     }
+    if (nrm && (s = dev_reserve(c, c->nrm, 36ull * n)) != VMN_OK) return s;
+    if (uv && (s = dev_reserve(c, c->uv, 24ull * n)) != VMN_OK) return s;
+    if (nrm && n) VMN_CUDA(c, cudaMemcpyAsync(c->nrm.p, nrm, 36ull * n, cudaMemcpyHostToDevice, attr_stream));
+    if (uv && n) VMN_CUDA(c, cudaMemcpyAsync(c->uv.p, uv, 24ull * n, cudaMemcpyHostToDevice, attr_stream));
     c->n_tris = n;
-    c->geometry_status = build_geometry(c); // synchronises the main stream; a failure is reported by vmn_scene_commit
-    c->geometry_err = c->geometry_status == VMN_OK ? std::string() : c->err;
-    c->geometry_built = true;
+    if (overlap) {
+        c->geometry_status = build_geometry(c); // synchronises the main stream; a failure is reported by vmn_scene_commit
+        c->geometry_err = c->geometry_status == VMN_OK ? std::string() : c->err;
+        c->geometry_built = true;
+    }
     if (c->copy_stream) VMN_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     VMN_CUDA(c, cudaStreamSynchronize(c->stream)); // host pointers are borrowed for the call only
     return VMN_OK;

@@ -169,25 +169,27 @@ inline uint32_t cdiv64(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) /
 
 // ---- collectives over the group (NCCL, or peer copies inside one process) ------------------------------------------------------
 // broadcast `bytes` from the root member's buffer to the same buffer of every other member; ptr(member) gives the buffer
+// (on_copy_stream: issue it on the members' copy streams instead of their main ones — the scene attributes, beside the geometry build)
 template <class P>
-vmn_status bcast(vmn_dist* g, P ptr, size_t bytes) {
+vmn_status bcast(vmn_dist* g, P ptr, size_t bytes, bool on_copy_stream = false) {
     if (g->world == 1 || bytes == 0) return VMN_OK;
+    auto stream_of = [&](vmn_dist::Member& mb) { return on_copy_stream ? mb.ctx->copy_stream : mb.ctx->stream; };
     if (g->use_nccl) {
         if (g->m.size() > 1) DNCCL(g, g_nccl.GroupStart());
         for (auto& mb : g->m) {
             DCUDA(g, cudaSetDevice(mb.device));
-            DNCCL(g, g_nccl.Broadcast(ptr(mb), ptr(mb), bytes, ncclUint8, 0, mb.comm, mb.ctx->stream));
+            DNCCL(g, g_nccl.Broadcast(ptr(mb), ptr(mb), bytes, ncclUint8, 0, mb.comm, stream_of(mb)));
         }
         if (g->m.size() > 1) DNCCL(g, g_nccl.GroupEnd());
         return VMN_OK;
     }
     auto* r = g->root();
     DCUDA(g, cudaSetDevice(r->device));
-    DCUDA(g, cudaStreamSynchronize(r->ctx->stream));
+    DCUDA(g, cudaStreamSynchronize(stream_of(*r)));
     for (auto& mb : g->m) {
         if (mb.rank == 0) continue;
         DCUDA(g, cudaSetDevice(mb.device));
-        DCUDA(g, cudaMemcpyPeerAsync(ptr(mb), mb.device, ptr(*r), r->device, bytes, mb.ctx->stream));
+        DCUDA(g, cudaMemcpyPeerAsync(ptr(mb), mb.device, ptr(*r), r->device, bytes, stream_of(mb)));
     }
     return VMN_OK;
 }
@@ -404,18 +406,47 @@ vmn_status vmn_dist_scene_set_triangles(vmn_dist* g, const float* pos, const flo
             (have_uv && (s = dev_reserve(c, c->uv, 24ull * nn)) != VMN_OK))
             return member_fail(g, mb, s, "scene staging");
         c->have_nrm = have_nrm; c->have_uv = have_uv;
+        if (!c->copy_stream) DCUDA(g, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         if (mb.rank == 0 && nn) {
             DCUDA(g, cudaEventRecord(g->ev[0], c->stream));
             DCUDA(g, cudaMemcpyAsync(c->pos.p, pos, 36ull * nn, cudaMemcpyHostToDevice, c->stream));
-            if (have_nrm) DCUDA(g, cudaMemcpyAsync(c->nrm.p, nrm, 36ull * nn, cudaMemcpyHostToDevice, c->stream));
-            if (have_uv) DCUDA(g, cudaMemcpyAsync(c->uv.p, uv, 24ull * nn, cudaMemcpyHostToDevice, c->stream));
         }
     }
+    // Positions first, on the main streams: as soon as they have arrived every member builds the position-only part of its BVH, while
+    // the normals and uvs go up on the root's copy stream and cross NVLink on the members' copy streams (same order on every rank).
     vmn_status s;
+    const bool overlap = load_overlap();
     if ((s = bcast(g, [](vmn_dist::Member& mb) { return mb.ctx->pos.p; }, 36ull * nn)) != VMN_OK) return s;
-    if (have_nrm && (s = bcast(g, [](vmn_dist::Member& mb) { return mb.ctx->nrm.p; }, 36ull * nn)) != VMN_OK) return s;
-    if (have_uv && (s = bcast(g, [](vmn_dist::Member& mb) { return mb.ctx->uv.p; }, 24ull * nn)) != VMN_OK) return s;
-    if (root && nn) DCUDA(g, cudaEventRecord(g->ev[1], root->ctx->stream));
+    for (auto& mb : g->m) {
+        DCUDA(g, cudaSetDevice(mb.device));
+        vmn_ctx* c = mb.ctx;
+        if (overlap) {
+            DCUDA(g, cudaEventRecord(c->ev[6], c->stream));
+            DCUDA(g, cudaStreamWaitEvent(c->copy_stream, c->ev[6], 0));
+        }
+        if (mb.rank == 0 && nn) {
+            cudaStream_t as = overlap ? c->copy_stream : c->stream;
+            if (have_nrm) DCUDA(g, cudaMemcpyAsync(c->nrm.p, nrm, 36ull * nn, cudaMemcpyHostToDevice, as));
+            if (have_uv) DCUDA(g, cudaMemcpyAsync(c->uv.p, uv, 24ull * nn, cudaMemcpyHostToDevice, as));
+        }
+    }
+    if (have_nrm && (s = bcast(g, [](vmn_dist::Member& mb) { return mb.ctx->nrm.p; }, 36ull * nn, overlap)) != VMN_OK) return s;
+    if (have_uv && (s = bcast(g, [](vmn_dist::Member& mb) { return mb.ctx->uv.p; }, 24ull * nn, overlap)) != VMN_OK) return s;
+    for (auto& mb : g->m) mb.ctx->n_tris = nn;
+    if (overlap) s = for_members(g, [&](vmn_dist::Member& mb) { // synchronises each main stream; a failed build is reported by vmn_dist_scene_commit
+        vmn_ctx* c = mb.ctx;
+        c->geometry_status = build_geometry(c);
+        c->geometry_err = c->geometry_status == VMN_OK ? std::string() : c->err;
+        c->geometry_built = true;
+        return VMN_OK;
+    });
+    if (s != VMN_OK) return s;
+    for (auto& mb : g->m) { // the main stream joins the copy stream: everything of this scene is ordered before what follows on it
+        DCUDA(g, cudaSetDevice(mb.device));
+        DCUDA(g, cudaEventRecord(mb.ctx->ev[7], mb.ctx->copy_stream));
+        DCUDA(g, cudaStreamWaitEvent(mb.ctx->stream, mb.ctx->ev[7], 0));
+    }
+    if (root && nn) { DCUDA(g, cudaSetDevice(root->device)); DCUDA(g, cudaEventRecord(g->ev[1], root->ctx->stream)); }
     if ((s = sync_all(g)) != VMN_OK) return s; // host pointers are borrowed for the call only
     if (root && nn) { float ms = 0.f; cudaEventElapsedTime(&ms, g->ev[0], g->ev[1]); g->stats.scene_ms = ms; }
     for (auto& mb : g->m) mb.ctx->n_tris = nn;

@@ -88,6 +88,8 @@ vmn_status check_device_error(vmn_ctx* c); // synchronises the stream; VMN_ERR_S
     } while (0)
 
 // bvh_build.cu
+// VMN_LOAD_OVERLAP=0 (read at every scene load): upload everything first and build in vmn_scene_commit, as before r02x (A/B switch)
+inline bool load_overlap() { const char* e = getenv("VMN_LOAD_OVERLAP"); return !(e && e[0] == '0'); }
 vmn_status build_bvh(vmn_ctx* c);      // = build_geometry + build_records
 vmn_status build_geometry(vmn_ctx* c); // positions only
 vmn_status build_records(vmn_ctx* c);  // + normals, uvs
