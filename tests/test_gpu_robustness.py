@@ -81,6 +81,37 @@ def test_checked_build_runs_every_kernel_without_a_bounds_violation():
     assert r.returncode == 0 and "all kernels ran" in r.stdout, r.stdout[-3000:]
 
 
+def test_pipelined_scene_load_equals_the_serial_load(monkeypatch):
+    """vmn_scene_set_triangles builds the position-only part of the BVH beside the upload of the normals and uvs, a group broadcasts the
+    positions first (r02x/y); VMN_LOAD_OVERLAP=0 is the serial load. Same tree, same film — also when a context is reloaded with a scene of
+    another size and back (grow-only staging buffers, the stashed build status)."""
+    a = scenes.spheres(2, 1, 4, 150.0)
+    b = scenes.spheres(1, 1, 3, 90.0)
+    cam = engine.camera_from_settings(320, 200, (0.0, 500.0, 1900.0), (0.0, 0.0, 0.0), 6.0, (3.6, 3.6 * 200 / 320), 8)
+    got = {}
+    for v in ("1", "0"):
+        monkeypatch.setenv("VMN_LOAD_OVERLAP", v)
+        with engine.Engine(device=0) as e:
+            frames = []
+            for scene in (a, b, a):
+                e.set_scene(*scene)
+                e.set_camera(cam)
+                e.render(mode=engine.MODE_FIXED, seed=5)
+                st = e.stats()
+                frames.append((e.read_image(), st["n_wide_nodes"], st["wide_depth"], st["rays_traced"]))
+            assert np.array_equal(frames[0][0], frames[2][0]) and frames[0][1:] == frames[2][1:]
+            assert e.stats()["build_ms"] > 0
+            got[v] = frames
+        with engine.DistGroup.local([0, 0], max_paths=1 << 20) as g:
+            g.set_scene(*a, broadcast=True)
+            g.set_camera(cam)
+            g.render(mode=engine.MODE_FIXED, seed=5, split=engine.DIST_SPLIT_TILES)
+            got["g" + v] = g.read_image()
+    for fa, fb in zip(got["1"], got["0"]):
+        assert np.array_equal(fa[0], fb[0]) and fa[1:] == fb[1:]
+    assert np.array_equal(got["g1"], got["g0"]) and np.array_equal(got["g1"], got["1"][0][0])
+
+
 def test_render_distributed_orders_the_collective_for_a_default_stream_engine():
     import torch
     import torch.distributed as dist
