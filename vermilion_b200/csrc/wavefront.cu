@@ -70,6 +70,11 @@ static vmn_status pool_ensure(vmn_ctx* c, uint64_t paths) {
     PathPool* p = c->pool;
     vmn_status s;
     if (paths > p->capacity) {
+        // A pool at or above half of max_paths is allocated at max_paths at once: two frames whose (pixels x samples per batch) products
+        // differ by a percent must not free and reallocate the whole pool inside a render (r02z: C2 then C4 at 8 GPUs, 132.7 M then
+        // 133.7 M paths of a 134.2 M cap = 15 GB freed and allocated again, +97 ms on the timed C4 frame).
+        const uint64_t cap = c->max_paths < 0xFFFFFFF0ull ? c->max_paths : 0xFFFFFFF0ull;
+        if (paths <= cap && paths * 2 >= cap) paths = cap;
         if ((s = dev_alloc(c, p->ray[0], 32 * paths)) != VMN_OK) return s;
         if ((s = dev_alloc(c, p->ray[1], 32 * paths)) != VMN_OK) return s;
         if ((s = dev_alloc(c, p->hit, 8 * paths)) != VMN_OK) return s;
