@@ -101,6 +101,9 @@ struct RoundParams {
 
 constexpr uint32_t kThrWritten = 0x8000u; // path meta bit 15: thr[slot] holds the throughput (otherwise it is exactly (1,1,1,1))
 
+#ifndef VMN_RAYGEN_DIRECT
+#define VMN_RAYGEN_DIRECT 1
+#endif
 __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, RoundParams rp, const uint32_t* __restrict__ cstate,
                                                      float4* __restrict__ rays, uint32_t* __restrict__ qcount, float4* __restrict__ radiance,
                                                      uint32_t* __restrict__ meta) {
@@ -110,8 +113,10 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
     uint64_t pixel = 0;
     uint32_t sample = 0, sxy = 0;
     if (live) {
-        const uint64_t lp = idx % rp.n_local;
-        const uint32_t k = (uint32_t)(idx / rp.n_local);
+        // (pixel, sample) of a slot with a 32-bit divide whenever the round fits 32 bits (queue slots are 32-bit, so it always does)
+        uint64_t lp; uint32_t k;
+        if ((total >> 32) == 0) { k = (uint32_t)idx / (uint32_t)rp.n_local; lp = (uint32_t)idx - k * (uint32_t)rp.n_local; }
+        else { lp = idx % rp.n_local; k = (uint32_t)(idx / rp.n_local); }
         sample = rp.s0 + k;
         live = map_pixel(pm, rp.lp0 + lp, &pixel);
         if (live) {
@@ -132,6 +137,17 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
         const float jx = rng.jitter(), jy = rng.jitter();
         camera_ray(cam, pixel, (sxy >> 1) & 1u, sxy & 1u, jx, jy, &o, &d);
     }
+#if VMN_RAYGEN_DIRECT
+    // A FIXED round over a contiguous pixel range has no dead slots: path idx goes to queue slot idx, no atomics, rays in pixel order.
+    if (rp.mode == VMN_MODE_FIXED && pm.tile == 0u) {
+        if (idx == 0) *qcount = (uint32_t)total;
+        if (live) {
+            st_stream(&rays[2ull * idx], make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx)));
+            st_stream(&rays[2ull * idx + 1], make_float4(d.x, d.y, d.z, 0.f));
+        }
+        return;
+    }
+#endif
     // warp-aggregated append
     const uint32_t ballot = __ballot_sync(0xffffffffu, live);
     if (ballot == 0u) return;
