@@ -28,8 +28,10 @@ struct CamDev {
 
 // pathtracer.cpp:251-280 (types follow the C++ promotions: the 0.25 / 0.5 literals are double)
 __device__ __forceinline__ void camera_ray(const CamDev& c, uint64_t p, uint32_t sampleX, uint32_t sampleY, float jx, float jy, V3* o, V3* d) {
-    float hx = (float)((((double)(float(p % c.width) + (sampleX * 0.5f - 0.5f) + jx) - 0.25) / (double)c.width) - 0.5);
-    float hy = (float)((((double)(float(p / c.width) + (sampleY * 0.5f - 0.5f) + jy) - 0.25) / (double)c.height) - 0.5);
+    uint64_t py = p / c.width, px = p - py * c.width;
+    if ((p >> 32) == 0) { const uint32_t y32 = (uint32_t)p / c.width; py = y32; px = (uint32_t)p - y32 * c.width; } // one 32-bit divide
+    float hx = (float)((((double)(float(px) + (sampleX * 0.5f - 0.5f) + jx) - 0.25) / (double)c.width) - 0.5);
+    float hy = (float)((((double)(float(py) + (sampleY * 0.5f - 0.5f) + jy) - 0.25) / (double)c.height) - 0.5);
     float bx = hx * c.sx, by = hy * c.sy;
     float g0 = bx, g1 = -by, g2 = -c.dist, g3 = 1.0f;
     float rd[4];
@@ -815,8 +817,10 @@ struct BfParams {
 
 // integrators.cpp:65-81
 __device__ __forceinline__ void bf_camera_ray(const CamDev& c, uint64_t p, float jx, float jy, V3* o, V3* d) {
-    float hx = (float)((((double)(float(p % c.width) + jx) - 0.25) / (double)c.width) * 2 - 1);
-    float hy = (float)((((double)(float(p / c.width) + jy) - 0.25) / (double)c.height) * 2 - 1);
+    uint64_t py = p / c.width, px = p - py * c.width;
+    if ((p >> 32) == 0) { const uint32_t y32 = (uint32_t)p / c.width; py = y32; px = (uint32_t)p - y32 * c.width; }
+    float hx = (float)((((double)(float(px) + jx) - 0.25) / (double)c.width) * 2 - 1);
+    float hy = (float)((((double)(float(py) + jy) - 0.25) / (double)c.height) * 2 - 1);
     float bx = (float)((double)(hx * c.sx) * 0.5), by = (float)((double)(hy * c.sy) * 0.5);
     float g0 = bx, g1 = -by, g2 = -c.dist, g3 = 1.0f;
     float rd[4];
