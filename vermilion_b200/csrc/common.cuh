@@ -139,19 +139,51 @@ struct PixelMap {
     uint32_t width, height;
     uint64_t begin;       // contiguous: first pixel
     uint32_t tile, rank, world, tiles_x;
+    uint32_t tile_log2p1; // log2(tile) + 1 when the tile size is a power of two (the usual 64: shifts instead of three divides), else 0
 };
+inline uint32_t tile_log2p1(uint32_t tile) { // host side, when a PixelMap is made
+    if (tile == 0 || (tile & (tile - 1))) return 0;
+    uint32_t l = 0;
+    while ((1u << l) < tile) ++l;
+    return l + 1;
+}
 
 __device__ __forceinline__ bool map_pixel(const PixelMap& m, uint64_t lp, uint64_t* pixel) {
     if (m.tile == 0) { *pixel = m.begin + lp; return *pixel < (uint64_t)m.width * m.height; }
     const uint32_t tt = m.tile * m.tile;
-    uint64_t j; uint32_t w;
-    if ((lp >> 32) == 0) { const uint32_t j32 = (uint32_t)lp / tt; j = j32; w = (uint32_t)lp - j32 * tt; } // the usual case: 32-bit divides
-    else { j = lp / tt; w = (uint32_t)(lp % tt); }
+    uint64_t j; uint32_t w, wx, wy;
+    if (m.tile_log2p1) { // power-of-two tile: shifts and masks
+        const uint32_t sh = m.tile_log2p1 - 1u;
+        j = lp >> (2u * sh); w = (uint32_t)lp & (tt - 1u); wx = w & (m.tile - 1u); wy = w >> sh;
+    } else {
+        if ((lp >> 32) == 0) { const uint32_t j32 = (uint32_t)lp / tt; j = j32; w = (uint32_t)lp - j32 * tt; } // the usual case: 32-bit divides
+        else { j = lp / tt; w = (uint32_t)(lp % tt); }
+        wy = w / m.tile; wx = w - wy * m.tile;
+    }
     const uint64_t t = j * m.world + m.rank;
     uint32_t ty, tx;
     if ((t >> 32) == 0) { ty = (uint32_t)t / m.tiles_x; tx = (uint32_t)t - ty * m.tiles_x; }
     else { ty = (uint32_t)(t / m.tiles_x); tx = (uint32_t)(t % m.tiles_x); }
-    const uint32_t x = tx * m.tile + (w % m.tile), y = ty * m.tile + (w / m.tile);
+    const uint32_t x = tx * m.tile + wx, y = ty * m.tile + wy;
+    if (x >= m.width || y >= m.height) return false;
+    *pixel = (uint64_t)y * m.width + x;
+    return true;
+}
+
+// Tile mode only: map_pixel plus the local tile index and the pixel's rank among the LIVE pixels of its tile (row-major over the part of
+// the tile inside the image) — what k_raygen needs to place a path in the queue without an atomic (live pixels before it = prefix[tile] + rank).
+__device__ __forceinline__ bool map_pixel_tile(const PixelMap& m, uint32_t lp, uint64_t* pixel, uint32_t* tile_j, uint32_t* rank_in_tile) {
+    const uint32_t tt = m.tile * m.tile;
+    uint32_t j, w, wx, wy;
+    if (m.tile_log2p1) { const uint32_t sh = m.tile_log2p1 - 1u; j = lp >> (2u * sh); w = lp & (tt - 1u); wx = w & (m.tile - 1u); wy = w >> sh; }
+    else { j = lp / tt; w = lp - j * tt; wy = w / m.tile; wx = w - wy * m.tile; }
+    const uint64_t t = (uint64_t)j * m.world + m.rank;
+    uint32_t ty, tx;
+    if ((t >> 32) == 0) { ty = (uint32_t)t / m.tiles_x; tx = (uint32_t)t - ty * m.tiles_x; }
+    else { ty = (uint32_t)(t / m.tiles_x); tx = (uint32_t)(t % m.tiles_x); }
+    const uint32_t x = tx * m.tile + wx, y = ty * m.tile + wy;
+    const uint32_t left = m.width - tx * m.tile, lw = left < m.tile ? left : m.tile; // live width of this tile
+    *tile_j = j; *rank_in_tile = wy * lw + wx;
     if (x >= m.width || y >= m.height) return false;
     *pixel = (uint64_t)y * m.width + x;
     return true;

@@ -162,7 +162,7 @@ uint64_t tiles_local_pixels(uint32_t width, uint32_t height, uint32_t tile, uint
 }
 PixelMap tile_map(uint32_t width, uint32_t height, uint32_t tile, uint32_t rank, uint32_t world) {
     PixelMap pm{};
-    pm.width = width; pm.height = height; pm.tile = tile; pm.rank = rank; pm.world = world; pm.tiles_x = (width + tile - 1) / tile;
+    pm.width = width; pm.height = height; pm.tile = tile; pm.rank = rank; pm.world = world; pm.tiles_x = (width + tile - 1) / tile; pm.tile_log2p1 = tile_log2p1(tile);
     return pm;
 }
 inline uint32_t cdiv64(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }

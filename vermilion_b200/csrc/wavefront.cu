@@ -52,6 +52,9 @@ struct PathPool {
     DevBuf ctl;       // uint32 counters: [0..1] queue counts, [8..] claim counters (unsigned long long)
     DevBuf cstate;    // COMPAT per-local-pixel stratum state
     DevBuf bf_last;   // BRUTEFORCE per-local-pixel lastSampleColour (float4)
+    DevBuf tile_prefix; // tile mode, FIXED: live pixels in the local tiles before tile j (uint32 per local tile), see k_raygen
+    uint32_t tile_live = 0;            // live pixels in all local tiles
+    uint32_t tile_key[5] = {0, 0, 0, 0, 0}; // (width, height, tile, rank, world) the table was made for
     uint32_t* h_count = nullptr; // pinned
     std::vector<cudaEvent_t> events;
     size_t ev_used = 0;
@@ -60,7 +63,7 @@ struct PathPool {
 void pool_destroy(vmn_ctx* c) {
     PathPool* p = c->pool;
     if (!p) return;
-    for (DevBuf* b : {&p->ray[0], &p->ray[1], &p->hit, &p->radiance, &p->thr, &p->meta, &p->ctl, &p->cstate, &p->bf_last}) dev_free(*b);
+    for (DevBuf* b : {&p->ray[0], &p->ray[1], &p->hit, &p->radiance, &p->thr, &p->meta, &p->ctl, &p->cstate, &p->bf_last, &p->tile_prefix}) dev_free(*b);
     if (p->h_count) cudaFreeHost(p->h_count);
     for (auto e : p->events) cudaEventDestroy(e);
     delete p;
@@ -108,18 +111,26 @@ constexpr uint32_t kThrWritten = 0x8000u; // path meta bit 15: thr[slot] holds t
 #endif
 __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, RoundParams rp, const uint32_t* __restrict__ cstate,
                                                      float4* __restrict__ rays, uint32_t* __restrict__ qcount, float4* __restrict__ radiance,
-                                                     uint32_t* __restrict__ meta) {
+                                                     uint32_t* __restrict__ meta, const uint32_t* __restrict__ tile_prefix, uint32_t tile_live) {
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t total = rp.n_local * rp.batch;
     bool live = idx < total;
     uint64_t pixel = 0;
     uint32_t sample = 0, sxy = 0;
+    uint32_t qdirect = 0; // tile mode with a prefix table: this path's queue position
     if (live) {
         // (pixel, sample) of a slot with a 32-bit divide whenever the round fits 32 bits (queue slots are 32-bit, so it always does)
         uint64_t lp; uint32_t k;
         if ((total >> 32) == 0) { k = (uint32_t)idx / (uint32_t)rp.n_local; lp = (uint32_t)idx - k * (uint32_t)rp.n_local; }
         else { lp = idx % rp.n_local; k = (uint32_t)(idx / rp.n_local); }
         sample = rp.s0 + k;
+#if VMN_RAYGEN_DIRECT
+        if (tile_prefix) {
+            uint32_t tj, rk;
+            live = map_pixel_tile(pm, (uint32_t)lp, &pixel, &tj, &rk);
+            qdirect = k * tile_live + __ldg(&tile_prefix[tj]) + rk;
+        } else
+#endif
         live = map_pixel(pm, rp.lp0 + lp, &pixel);
         if (live) {
             if (rp.mode == VMN_MODE_COMPAT) {
@@ -141,11 +152,14 @@ __global__ void __launch_bounds__(kWfBlock) k_raygen(CamDev cam, PixelMap pm, Ro
     }
 #if VMN_RAYGEN_DIRECT
     // A FIXED round over a contiguous pixel range has no dead slots: path idx goes to queue slot idx, no atomics, rays in pixel order.
-    if (rp.mode == VMN_MODE_FIXED && pm.tile == 0u) {
-        if (idx == 0) *qcount = (uint32_t)total;
+    // Tiles: the live pixels before a path are known in closed form from a per-tile prefix table (only the image's last tile row and
+    // column are partial), so its queue position is too.
+    if (rp.mode == VMN_MODE_FIXED && (pm.tile == 0u || tile_prefix)) {
+        const uint64_t q = pm.tile == 0u ? idx : (uint64_t)qdirect;
+        if (idx == 0) *qcount = pm.tile == 0u ? (uint32_t)total : tile_live * rp.batch;
         if (live) {
-            st_stream(&rays[2ull * idx], make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx)));
-            st_stream(&rays[2ull * idx + 1], make_float4(d.x, d.y, d.z, 0.f));
+            st_stream(&rays[2ull * q], make_float4(o.x, o.y, o.z, __uint_as_float((uint32_t)idx)));
+            st_stream(&rays[2ull * q + 1], make_float4(d.x, d.y, d.z, 0.f));
         }
         return;
     }
@@ -649,6 +663,7 @@ vmn_status make_pixel_map(vmn_ctx* c, const vmn_render_params* prm, PixelMap* ou
         if (!prm->tile_world || prm->tile_rank >= prm->tile_world) return fail(c, VMN_ERR_INVALID, "bad tile rank/world");
         pm.tile = prm->tile_size; pm.rank = prm->tile_rank; pm.world = prm->tile_world;
         pm.tiles_x = (pm.width + pm.tile - 1) / pm.tile;
+        pm.tile_log2p1 = tile_log2p1(pm.tile);
         const uint64_t tiles = (uint64_t)pm.tiles_x * ((pm.height + pm.tile - 1) / pm.tile);
         const uint64_t mine = tiles > pm.rank ? (tiles - pm.rank + pm.world - 1) / pm.world : 0;
         *n_local_total = mine * pm.tile * pm.tile;
@@ -710,6 +725,32 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
     clk.flush();
     VMN_CUDA(c, cudaMemsetAsync(p->ctl.as<char>() + kOffFrame, 0, 32, c->stream));
 
+    // FIXED rounds over tiles: the per-tile prefix of live pixels that lets k_raygen place every path without an atomic (single chunk only;
+    // made once per (image, tile, rank, world) and kept in the pool)
+    const uint32_t* tile_prefix = nullptr;
+#if VMN_RAYGEN_DIRECT
+    if (mode == VMN_MODE_FIXED && pm.tile && chunk == n_local_total && n_local_total < 0xFFFFFFFFull) {
+        const uint32_t key[5] = {pm.width, pm.height, pm.tile, pm.rank, pm.world};
+        const uint32_t tt = pm.tile * pm.tile, ntiles = (uint32_t)(n_local_total / tt);
+        if (memcmp(key, p->tile_key, sizeof(key)) != 0 || !p->tile_prefix.p) {
+            std::vector<uint32_t> pre(ntiles);
+            uint32_t run = 0;
+            for (uint32_t j = 0; j < ntiles; ++j) {
+                const uint64_t t = (uint64_t)j * pm.world + pm.rank;
+                const uint32_t ty = (uint32_t)(t / pm.tiles_x), tx = (uint32_t)(t % pm.tiles_x);
+                const uint32_t lw = std::min(pm.tile, pm.width - tx * pm.tile), lh = std::min(pm.tile, pm.height - ty * pm.tile);
+                pre[j] = run;
+                run += lw * lh;
+            }
+            if ((s = dev_reserve(c, p->tile_prefix, 4ull * ntiles)) != VMN_OK) return s;
+            VMN_CUDA(c, cudaMemcpyAsync(p->tile_prefix.p, pre.data(), 4ull * ntiles, cudaMemcpyHostToDevice, c->stream)); // pageable: staged before it returns
+            p->tile_live = run;
+            memcpy(p->tile_key, key, sizeof(key));
+        }
+        tile_prefix = p->tile_prefix.as<uint32_t>();
+    }
+#endif
+
     VMN_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
     for (uint64_t lp0 = 0; lp0 < n_local_total; lp0 += chunk) {
         RoundParams rp{};
@@ -725,7 +766,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 VMN_CUDA(c, cudaMemsetAsync(p->ctl.p, 0, 64 + 8 * kMaxClaims, c->stream));
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, p->cstate.as<uint32_t>(), p->ray[0].as<float4>(), qc,
-                                                                                   p->radiance.as<float4>(), p->meta.as<uint32_t>());
+                                                                                   p->radiance.as<float4>(), p->meta.as<uint32_t>(), nullptr, 0u);
                 clk.end();
                 ++c->stats.kernel_launches;
                 clk.flush();
@@ -766,7 +807,7 @@ vmn_status render_frame(vmn_ctx* c, const vmn_render_params* prm) {
                 clk.begin(ST_RAYGEN);
                 k_raygen<<<cdiv64(rp.n_local * rp.batch, kWfBlock), kWfBlock, 0, c->stream>>>(cd, pm, rp, nullptr, p->ray[0].as<float4>(), qc,
                                                                                               p->radiance.as<float4>(),
-                                                                                              p->meta.as<uint32_t>());
+                                                                                              p->meta.as<uint32_t>(), tile_prefix, p->tile_live);
                 clk.end();
                 ++c->stats.kernel_launches;
                 int cur = 0;
