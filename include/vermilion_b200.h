@@ -163,6 +163,16 @@ vmn_status vmn_scene_commit(vmn_ctx* ctx); /* finishes the GPU BVH build (all of
 /* replaces BVH::getIntersection(ray, &info, false) (bvh.cpp:47-145) for n rays */
 vmn_status vmn_intersect(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, vmn_hit* out, uint32_t flags);
 vmn_status vmn_intersect_device(vmn_ctx* ctx, const vmn_ray* d_rays, uint64_t n, vmn_hit* d_out, uint32_t flags);
+/* vmn_intersect for callers that may not allocate (code under CUDA graph capture nearby, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments, same kernels and
+ * bit-identical results as vmn_intersect (host rays in, host hits out), but every byte of device scratch — the persistent kernel's
+ * ray-claim cursor and visit counters, the staged rays, the hits — lives in one file-scope `static __device__` array of the library
+ * (3 MiB + 256 B, held by every GPU that loads the library until exit) instead of the context's grow-only cudaMalloc buffers: the
+ * call makes no cudaMalloc / cudaFree and calls no allocating routine. n > VMN_STATIC_MAX_RAYS is rejected with VMN_ERR_INVALID (the
+ * message names the limit). All calls on one GPU share the array; it keeps the previous call's contents (the call clears the counter
+ * block itself), and calls that overlap on the GPU — two contexts or two host threads on one device — race on it: serialise them. */
+#define VMN_STATIC_MAX_RAYS 65536u
+vmn_status vmn_intersect_static(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, vmn_hit* out, uint32_t flags);
 /* replaces MeshEngine::RayCastCollision (meshEngine.cpp:196-207): out[i] = 1 iff closest hit has t > 1e-3 */
 vmn_status vmn_occluded(vmn_ctx* ctx, const vmn_ray* rays, uint64_t n, uint8_t* out);
 /* replaces MeshEngine::RayCast (meshEngine.cpp:239-509) for n rays */

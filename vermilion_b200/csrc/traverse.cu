@@ -7,6 +7,8 @@
 #include "engine.cuh"
 #include "traverse.cuh"
 
+#include <mutex>
+
 namespace vmn {
 
 constexpr int kTraceBlock = 128;
@@ -174,3 +176,83 @@ vmn_status launch_raycast(vmn_ctx* c, const vmn_ray* d_rays, uint64_t n, vmn_ray
 }
 
 } // namespace vmn
+
+// ---- vmn_intersect_static: closest-hit queries for callers that may not allocate -------------------------------------------------
+// No counterpart in the reference (declared in include/vermilion_b200.h). It is
+// vmn_intersect — host rays in, host hits out, the same k_intersect instantiations — with ALL device scratch (the persistent kernel's
+// claim cursor + visit counters, the staged rays, the hits) in one file-scope __device__ array instead of the context's grow-only
+// cudaMalloc buffers. Every device that loads the library holds the array (3 MiB + 256 B) until exit. Calls share it: it keeps the last
+// call's contents (the counter block is cleared on the stream at the start of each call; rays and hits are overwritten before they are
+// read), and two calls that overlap on one GPU — two contexts, two host threads — race on it.
+namespace {
+
+constexpr uint64_t kStaticCounterBytes = 256; // claim cursor (u64), pad, TravCounters: the first 64 bytes in use, like vmn_ctx::counters
+constexpr uint64_t kStaticRayOff = kStaticCounterBytes;
+constexpr uint64_t kStaticHitOff = kStaticRayOff + sizeof(vmn_ray) * (uint64_t)VMN_STATIC_MAX_RAYS;
+constexpr uint64_t kStaticBytes = kStaticHitOff + sizeof(vmn_hit) * (uint64_t)VMN_STATIC_MAX_RAYS;
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kStaticMaxDevices = 64;
+unsigned char* g_static_ptr[kStaticMaxDevices] = {};
+std::mutex g_static_mu;
+
+vmn_status static_scratch(vmn_ctx* c, unsigned char** out) {
+    if (c->device < 0 || c->device >= kStaticMaxDevices) return vmn::fail(c, VMN_ERR_INVALID, "device %d: the static scratch serves devices 0..%d", c->device, kStaticMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[c->device]) {
+        VMN_CUDA(c, cudaSetDevice(c->device));
+        void* p = nullptr;
+        VMN_CUDA(c, cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return vmn::fail(c, VMN_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_ptr[c->device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_ptr[c->device];
+    return VMN_OK;
+}
+
+} // namespace
+
+extern "C" vmn_status vmn_intersect_static(vmn_ctx* c, const vmn_ray* rays, uint64_t n, vmn_hit* out, uint32_t flags) {
+    using namespace vmn;
+    if (!c) return VMN_ERR_INVALID;
+    if (!c->committed) return fail(c, VMN_ERR_STATE, "scene not committed (call vmn_scene_commit)");
+    if (n && (!rays || !out)) return fail(c, VMN_ERR_INVALID, "null ray/hit pointer");
+    if (n > (uint64_t)VMN_STATIC_MAX_RAYS)
+        return fail(c, VMN_ERR_INVALID, "vmn_intersect_static: %llu rays exceed VMN_STATIC_MAX_RAYS = %u (the static device scratch holds no more; "
+                    "split the batch or use vmn_intersect)", (unsigned long long)n, (unsigned)VMN_STATIC_MAX_RAYS);
+    VMN_CUDA(c, cudaSetDevice(c->device));
+    unsigned char* base = nullptr;
+    vmn_status s = static_scratch(c, &base);
+    if (s != VMN_OK) return s;
+    auto* next = reinterpret_cast<unsigned long long*>(base);
+    auto* gcnt = reinterpret_cast<TravCounters*>(next + 2);
+    auto* d_rays = reinterpret_cast<vmn_ray*>(base + kStaticRayOff);
+    auto* d_out = reinterpret_cast<vmn_hit*>(base + kStaticHitOff);
+    const bool count = (c->flags & VMN_CFG_COUNTERS) != 0;
+    const bool wide = !(flags & VMN_ISECT_BVH2);
+    c->stats.kernel_launches = 0;
+    c->stats.rays_traced = n;
+    if (n) {
+        VMN_CUDA(c, cudaMemsetAsync(base, 0, kStaticCounterBytes, c->stream)); // the cursor and the counters must start at zero
+        VMN_CUDA(c, cudaMemcpyAsync(d_rays, rays, sizeof(vmn_ray) * n, cudaMemcpyHostToDevice, c->stream));
+        VMN_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+#define LAUNCH(W, C)                                                                                                           \
+    k_intersect<W, C><<<resident_grid(c, k_intersect<W, C>), kTraceBlock, 0, c->stream>>>(c->scene, d_rays, n, d_out, next, gcnt, refill_min(c))
+        if (wide) { if (count) LAUNCH(true, true); else LAUNCH(true, false); }
+        else { if (count) LAUNCH(false, true); else LAUNCH(false, false); }
+#undef LAUNCH
+        VMN_CUDA(c, cudaGetLastError());
+        VMN_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+        c->stats.kernel_launches = 1;
+        VMN_CUDA(c, cudaMemcpyAsync(out, d_out, sizeof(vmn_hit) * n, cudaMemcpyDeviceToHost, c->stream));
+    }
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (n && count) VMN_CUDA(c, cudaMemcpyAsync(h, base, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    if ((s = check_device_error(c)) != VMN_OK) return s; // synchronises the stream; VMN_ERR_STATE if a traversal stack overflowed
+    if (n) { float ms = 0.f; cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->stats.extend_ms = ms; c->stats.total_ms = ms; }
+    if (count) { c->stats.nodes_visited = h[2]; c->stats.tris_tested = h[3]; }
+    return VMN_OK;
+}

@@ -25,6 +25,7 @@ CFG_COUNTERS = 1
 RENDER_ACCUMULATE = 1
 RENDER_BF_SHADOW = 2
 ISECT_BVH2 = 1
+STATIC_MAX_RAYS = 65536  # VMN_STATIC_MAX_RAYS
 STATUS = {0: "OK", 1: "INVALID", 2: "CUDA", 3: "OOM", 4: "STATE", 5: "NCCL"}
 DIST_SPLIT_SAMPLES, DIST_SPLIT_TILES = 0, 1
 DIST_SCENE_BROADCAST = 1
@@ -33,7 +34,7 @@ DIST_MAX_RANKS, DIST_ID_BYTES = 16, 128
 
 EXPORTS = ["vmn_abi_version", "vmn_create", "vmn_destroy", "vmn_last_error", "vmn_set_stream", "vmn_synchronize",
            "vmn_scene_set_triangles", "vmn_scene_set_spheres", "vmn_reference_spheres", "vmn_scene_set_texture",
-           "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_occluded", "vmn_raycast", "vmn_radiance",
+           "vmn_scene_commit", "vmn_intersect", "vmn_intersect_device", "vmn_intersect_static", "vmn_occluded", "vmn_raycast", "vmn_radiance",
            "vmn_camera_set", "vmn_camera_rays", "vmn_render", "vmn_read_image", "vmn_film_device",
            "vmn_film_resolve_device", "vmn_film_upload", "vmn_film_aux_device", "vmn_read_image_rgba8", "vmn_get_stats",
            "vmn_probe_read_bandwidth",
@@ -135,6 +136,7 @@ def load_library():
     L.vmn_scene_commit.argtypes = [vp]
     L.vmn_intersect.argtypes = [vp, vp, u64, vp, u32]
     L.vmn_intersect_device.argtypes = [vp, vp, u64, vp, u32]
+    L.vmn_intersect_static.argtypes = [vp, vp, u64, vp, u32]
     L.vmn_occluded.argtypes = [vp, vp, u64, vp]
     L.vmn_raycast.argtypes = [vp, vp, u64, vp]
     L.vmn_radiance.argtypes = [vp, vp, u64, u64, i32, u32, vp, vp]
@@ -248,6 +250,14 @@ class Engine:
 
     def intersect_device(self, d_rays_ptr, n, d_out_ptr, flags=0):
         self._chk(self.L.vmn_intersect_device(self.h, d_rays_ptr, n, d_out_ptr, flags), "vmn_intersect_device")
+
+    def intersect_static(self, rays, flags=0):
+        """vmn_intersect_static: as intersect(), with the device scratch in the library's static array (no allocation; at most
+        STATIC_MAX_RAYS rays per call)."""
+        rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
+        out = np.empty(len(rays), HIT)
+        self._chk(self.L.vmn_intersect_static(self.h, _p(rays), len(rays), _p(out), flags), "vmn_intersect_static")
+        return out
 
     def occluded(self, rays):
         rays = np.ascontiguousarray(rays).view(RAY).reshape(-1)
