@@ -65,3 +65,11 @@ def test_fails_loudly_without_cuda_device():
         pytest.skip("a CUDA device is present")
     with pytest.raises(engine.VmnError, match="no CUDA device|CUDA"):
         engine.Engine(device=0)
+
+
+def test_static_scratch_entry_point_rejects_a_null_context_without_touching_the_gpu():
+    """vmn_intersect_static (no reference counterpart; include/vermilion_b200.h) checks its context before anything else."""
+    lib = engine.load_library()
+    assert lib.vmn_intersect_static(None, None, 0, None, 0) == 1  # VMN_ERR_INVALID
+    src = open(HEADER).read()
+    assert "#define VMN_STATIC_MAX_RAYS 65536u" in src and engine.STATIC_MAX_RAYS == 65536

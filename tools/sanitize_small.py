@@ -5,7 +5,7 @@
   compute-sanitizer --tool racecheck python tools/sanitize_small.py
   compute-sanitizer --tool synccheck python tools/sanitize_small.py
 
-Touches build (k_prim_bounds .. k_collapse), k_intersect (BVH8 + BVH2, counting and not), k_occluded, k_raycast, vmn_radiance (both
+Touches build (k_prim_bounds .. k_collapse), k_intersect (BVH8 + BVH2, counting and not; also through vmn_intersect_static), k_occluded, k_raycast, vmn_radiance (both
 estimators), k_raygen / k_extend / k_shade / k_accumulate / k_resolve (FIXED, COMPAT, tiles, accumulate), the BRUTEFORCE kernels (with and
 without shadow rays, textured), k_pack_rgba8 and the bandwidth probe. Results are compared with the CPU oracle so that a sanitizer-clean
 run is also a correct one. Sizes are tiny: the sanitizer slows kernels down 10-100x."""
@@ -40,6 +40,8 @@ def main():
             h = e.intersect(rays)
             c = common.classify_hits(h, orc.intersect(rays))
             assert c["bad"] == 0 and c["t_exact"] == c["hits"], c
+            for _ in range(2):  # the static-scratch entry point (vmn_intersect_static), twice over the same array
+                assert np.array_equal(e.intersect_static(rays).view(np.uint8), h.view(np.uint8))
             assert np.array_equal(e.occluded(rays), orc.occluded(rays))
             rc = e.raycast(rays)
             assert (rc["flags"] & 1).mean() > 0.9
